@@ -1,0 +1,175 @@
+/* slamgpu.h — C ABI of the B200 FastSLAM backend (slam_b200/libslamgpu.so).
+ *
+ * This is the drop-in boundary.  It sits where the reference's FPGA AcceleratorHandler sits
+ * (src/backend/AcceleratorHandler.h:10-33: map device, getMemoryPointer/setN/start/isDone) but one
+ * level higher: instead of "one particle's Jacobians" the library owns the whole particle set on the
+ * device and exposes the FastSLAM1 / FastSLAM2 method entry points
+ *     predict(particles, xTrue, V, G, Q, dt)            algorithms/fastslam2.h:20-21, fastslam1.h:29-30
+ *     update(particles, zf, zn, idf, z, table, R)       algorithms/fastslam2.h:23-24, fastslam1.h:32-33
+ * with `particles` replaced by an opaque handle.  A literal computeJacobians drop-in with the FPGA
+ * float-record layout (core.cpp:586-664) is kept as slamgpu_compute_jacobians.
+ *
+ * Conventions
+ *   - every call returns 0 on success, a negative SLAMGPU_E* code otherwise; slamgpu_last_error()
+ *     gives the text.  Nothing throws across the ABI and nothing calls exit().
+ *   - the library owns all device memory; the caller owns every host buffer it passes; no host
+ *     pointer is retained after a call returns (except slamgpu_stage_noise's copy target on device).
+ *   - one caller thread per handle (the reference loop is single threaded).
+ *   - there is NO CPU fallback: without a CUDA device slamgpu_create fails with SLAMGPU_ENODEVICE.
+ *
+ * Flat state layout (all fp32, P = particles on this handle, Nf = landmarks held per particle):
+ *     xv[c*P+p]            c<3  pose (x, y, theta)                         Particle::_xv   Particle.h:46
+ *     Pv[(r*3+c)*P+p]           pose covariance planes, row-major 3x3      Particle::_Pv   Particle.h:47
+ *     w[p]                      weight                                     Particle::_w    Particle.h:45
+ *     lm_mean[(l*P+p)*2+j]      landmark mean,  l<Nf                       _landmarkXs     Particle.h:48
+ *     lm_cov[(l*P+p)*4+j]       landmark covariance, j = column-major linear index (P(0),P(1),P(2),P(3)
+ *                               exactly like the accelerator record, core.cpp:613-615)    Particle.h:49
+ */
+#ifndef SLAMGPU_H
+#define SLAMGPU_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SLAMGPU_OK 0
+#define SLAMGPU_EINVAL (-1)    /* bad argument */
+#define SLAMGPU_ENODEVICE (-2) /* no usable CUDA device: the library has no CPU path */
+#define SLAMGPU_ECUDA (-3)     /* a CUDA call failed; see slamgpu_last_error() */
+#define SLAMGPU_ENOMEM (-4)    /* device allocation failed */
+#define SLAMGPU_ECAP (-5)      /* landmark capacity (nf_cap) exceeded */
+#define SLAMGPU_ECOMM (-6)     /* multi-device exchange failed */
+
+#define SLAMGPU_FASTSLAM1 1
+#define SLAMGPU_FASTSLAM2 2
+
+/* Order of the floating-point sums behind the resampling CDF.
+ * REFERENCE: Eigen's SSE redux order for the weight sums and a sequential fp32 running sum for the CDF —
+ *            bit-identical to core.cpp:718-729,780-824; one thread, meant for the reference's own sizes.
+ * BLOCKED  : fixed-shape blocked scan (blocks of 1024, 32-lane Hillis-Steele ladders, recursive over
+ *            block totals) — the order used at scale; identical bits for any device count. */
+#define SLAMGPU_SCAN_REFERENCE 0
+#define SLAMGPU_SCAN_BLOCKED 1
+
+typedef struct slamgpu slamgpu_t;
+
+typedef struct slamgpu_config {
+    int64_t n_particles; /* NPARTICLES held by THIS handle (the local shard when sharded) */
+    int32_t nf_cap;      /* landmark rows reserved per particle */
+    int32_t method;      /* SLAMGPU_FASTSLAM1 / SLAMGPU_FASTSLAM2  (SLAMBackendApplication.cpp:26-29) */
+    float wheel_base;    /* WHEELBASE  (fastslam2wrapper.cpp:18-23) */
+    float sigma_phi;     /* sigmaT */
+    int32_t n_effective; /* NEFFECTIVE: resample when nEff < n_effective (core.cpp:739; int like the reference) */
+    int32_t use_heading; /* SWITCH_HEADING_KNOWN */
+    int32_t do_resample; /* SWITCH_RESAMPLE */
+    int32_t scan_mode;   /* SLAMGPU_SCAN_* */
+    int32_t device;      /* CUDA device ordinal */
+    int32_t spare_rows;  /* landmark rows kept free for the resample ring (0 = default) */
+    int32_t reserved[4];
+} slamgpu_config;
+
+const char *slamgpu_last_error(void);
+/* Library / build identification, e.g. "slamgpu 0.1 sm_100a". */
+const char *slamgpu_version(void);
+
+/* Replaces AcceleratorHandler::AcceleratorHandler / ~AcceleratorHandler (AcceleratorHandler.cpp:13-47):
+ * particles start as in ParticleSLAMWrapper::initializeParticles (w = 1/N, xv = 0, Pv = 0, no landmarks). */
+int slamgpu_create(const slamgpu_config *cfg, slamgpu_t **out);
+void slamgpu_destroy(slamgpu_t *h);
+
+/* The library launches everything on one stream.  Passing a caller-owned cudaStream_t (as void*) makes
+ * caller-side CUDA events see the work; NULL restores the internal stream. */
+int slamgpu_set_stream(slamgpu_t *h, void *cuda_stream);
+void *slamgpu_get_stream(slamgpu_t *h);
+int slamgpu_synchronize(slamgpu_t *h);
+
+/* Pinned host memory for callers that want true async copies (cudaHostAlloc / cudaFreeHost). */
+void *slamgpu_host_alloc(uint64_t bytes);
+void slamgpu_host_free(void *p);
+
+/* Whole-state transfer in the flat layout above (vector<Particle> <-> device).  Any pointer may be NULL
+ * to skip that field.  Nf rows of lm_* are moved. */
+int slamgpu_upload_particles(slamgpu_t *h, const float *xv, const float *Pv, const float *w, const float *lm_mean,
+                             const float *lm_cov, int32_t Nf);
+int slamgpu_download_particles(slamgpu_t *h, float *xv, float *Pv, float *w, float *lm_mean, float *lm_cov,
+                               int32_t *Nf);
+/* Synthetic workloads (the -SYNTH_* configurations): a tile of Pt particles in the flat layout (with P := Pt)
+ * is replicated on the device over all P particles, particle p taking tile particle p % Pt. */
+int slamgpu_upload_particles_tiled(slamgpu_t *h, int64_t Pt, const float *xv, const float *Pv, const float *w,
+                                   const float *lm_mean, const float *lm_cov, int32_t Nf);
+int slamgpu_landmark_count(slamgpu_t *h);
+
+/* FastSLAM{1,2}::predict (fastslam2.cpp:51-60,70-125; fastslam1.cpp:37-86): every particle.
+ * Q row-major 2x2.  phi_true = xTrue(2) (used when use_heading).  gauss: NULL (no predict noise) or host
+ * [2][P] standard normals, row 0 for V, row 1 for G, drawn like nRandMat::randn(2,1) per particle
+ * (core.cpp:383-419).  FastSLAM1 passes gauss (addPredictNoise is forced on, fastslam1wrapper.cpp:20). */
+int slamgpu_predict(slamgpu_t *h, float V, float G, const float Q[4], float dt, float phi_true,
+                    const float *gauss);
+
+/* FastSLAM{1,2}::update (fastslam2.cpp:21-48, fastslam1.cpp:18-35) = per-particle part + resampleParticles.
+ *   zf [K][2] range/bearing of known landmarks, idf [K] their (distinct) landmark rows, zn [Kn][2] new ones
+ *   (appended at rows Nf..Nf+Kn-1, core.cpp:479-509), R row-major 2x2.
+ *   gauss: host [3][P] standard normals for the FastSLAM2 pose sample (multivariateGauss, core.cpp:452-458);
+ *          ignored for FastSLAM1.  unif: host [P] doubles = rand()/double(RAND_MAX) (core.cpp:775-777),
+ *          consumed on every update like the reference.  Both may be NULL after slamgpu_stage_noise().
+ *   did_resample / neff (nullable) report the branch taken at core.cpp:739 and nEff. */
+int slamgpu_update(slamgpu_t *h, const float *zf, const int32_t *idf, int32_t K, const float *zn, int32_t Kn,
+                   const float R[4], const float *gauss, const double *unif, int32_t *did_resample, float *neff);
+
+/* The two halves of slamgpu_update, for step-level parity checks. */
+int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int32_t *idf, int32_t K, const float *zn,
+                             int32_t Kn, const float R[4], const float *gauss);
+/* resampleParticles (core.cpp:718-749).  keep_out: nullable host [P] ints = stratifiedResample's keep[]
+ * (global particle indices when sharded; -1 exactly where the reference leaves -1). */
+int slamgpu_resample(slamgpu_t *h, const double *unif, int32_t *keep_out, float *neff, int32_t *did_resample);
+
+/* Copies noise for the NEXT predict/update calls into device buffers so that those calls can be issued with
+ * gauss == NULL / unif == NULL and no host->device traffic (device-resident benchmarking, device RNG feeds).
+ * gauss_rows = 2 (predict) or 3 (FastSLAM2 update); either pointer may be NULL. */
+int slamgpu_stage_noise(slamgpu_t *h, const float *gauss, int32_t gauss_rows, const double *unif);
+
+/* computeJacobians, literal drop-in for the accelerator path (core.cpp:586-664), one particle:
+ *   in : xv[3], R(0..3) column-major linear, then n x { xf[2], Pf(0..3) column-major linear }   (7+6n floats)
+ *   out: n x { zp[2], Hf[4] row-major, Hv[6] row-major, Sf[4] row-major }                        (16n floats)
+ * h may be NULL (device 0, default stream). */
+int slamgpu_compute_jacobians(slamgpu_t *h, const float *in, int32_t n, float *out);
+/* The batched form over the resident particle set: out host [K][P][16] in the record order above. */
+int slamgpu_compute_jacobians_batch(slamgpu_t *h, const int32_t *idf, int32_t K, const float R[4], float *out);
+
+/* ParticleSLAMWrapper::computeEstimatedPosition (ParticleSLAMWrapper.cpp:56-77): mean x, mean y (double
+ * accumulation) and the heading of the first maximum-weight particle. */
+int slamgpu_estimate(slamgpu_t *h, double *x, double *y, double *t);
+/* Every stride-th particle's pose (and optionally its first Nf landmark means) for the plot feed
+ * (ParticleSLAMWrapper.cpp:34-54 sends all of them; that cannot scale to 1M particles).
+ * xv_out [3][n], lm_out [Nf][n][2] (nullable), n = ceil(P/stride). */
+int slamgpu_download_decimated(slamgpu_t *h, int64_t stride, float *xv_out, float *lm_out);
+
+/* Device-time accounting per kernel family (CUDA events on the launching stream). */
+#define SLAMGPU_T_PREDICT 0
+#define SLAMGPU_T_UPDATE 1   /* the per-particle update kernel (FastSLAM1 or FastSLAM2) */
+#define SLAMGPU_T_ADDFEAT 2
+#define SLAMGPU_T_WEIGHTS 3  /* weight sums, normalise, CDF, select, search */
+#define SLAMGPU_T_GATHER 4   /* resample gather of poses and landmark maps */
+#define SLAMGPU_T_ESTIMATE 5
+#define SLAMGPU_T_COUNT 6
+int slamgpu_timing_enable(slamgpu_t *h, int32_t on);
+/* Sums since the last reset; synchronises the stream.  launches = kernel launches of that family. */
+int slamgpu_timing_read(slamgpu_t *h, int32_t which, double *total_ms, int64_t *events, int64_t *launches);
+int slamgpu_timing_reset(slamgpu_t *h);
+/* Total kernel launches issued by this handle since creation. */
+int64_t slamgpu_launch_count(slamgpu_t *h);
+
+/* ---- sharding over several devices (one handle per device, one process per device) ------------------
+ * Particles are block-partitioned: rank r holds global particles [r*P, (r+1)*P).  predict / update_particles
+ * need no exchange.  Resampling exchanges (1) the per-1024-block weight totals (all-gather, rank order — the
+ * blocked scan is then bit-identical to the one-device run), (2) the CDF, and (3) migrates resampled
+ * particles.  The transport is NCCL; the caller distributes the 128-byte unique id. */
+int slamgpu_comm_unique_id(void *id128);
+int slamgpu_comm_init(slamgpu_t *h, int32_t rank, int32_t world, const void *id128);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SLAMGPU_H */

@@ -1,0 +1,790 @@
+// capi.cu — the C ABI of include/slamgpu.h: handle, device memory, launch sequencing.
+//
+// Everything per-particle happens in the kernels of kernels.cuh; this file only owns buffers, stages the small
+// per-step host inputs (observation set, controls), sequences launches on one stream and reads back the few
+// scalars the caller needs (nEff, the resample decision).  There is no host compute path: every entry point that
+// would need one fails with SLAMGPU_ENODEVICE when no CUDA device is present.
+#include "../../include/slamgpu.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "handle.h"
+#include "kernels.cuh"
+
+using namespace slam;
+
+static thread_local std::string g_err;
+int slam_fail(int code, const std::string &msg) {
+    g_err = msg;
+    return code;
+}
+// ---- timing helpers -------------------------------------------------------------------------------------
+static int span_begin(slamgpu *h, int which, TimedSpan *sp) {
+    sp->which = -1;
+    if (!h->timing) return SLAMGPU_OK;
+    for (int i = 0; i < 2; i++) {
+        cudaEvent_t e;
+        if (!h->free_events.empty()) {
+            e = h->free_events.back();
+            h->free_events.pop_back();
+        } else {
+            CU(cudaEventCreate(&e));
+        }
+        (i == 0 ? sp->a : sp->b) = e;
+    }
+    sp->which = which;
+    CU(cudaEventRecord(sp->a, h->stream));
+    return SLAMGPU_OK;
+}
+static int timing_flush(slamgpu *h) {
+    if (h->spans.empty()) return SLAMGPU_OK;
+    CU(cudaStreamSynchronize(h->stream));
+    for (auto &sp : h->spans) {
+        float ms = 0;
+        CU(cudaEventElapsedTime(&ms, sp.a, sp.b));
+        h->t_ms[sp.which] += ms;
+        h->t_events[sp.which]++;
+        h->free_events.push_back(sp.a);
+        h->free_events.push_back(sp.b);
+    }
+    h->spans.clear();
+    return SLAMGPU_OK;
+}
+static int span_end(slamgpu *h, TimedSpan *sp) {
+    if (sp->which < 0) return SLAMGPU_OK;
+    CU(cudaEventRecord(sp->b, h->stream));
+    h->spans.push_back(*sp);
+    if (h->spans.size() > 8192) RET(timing_flush(h));
+    return SLAMGPU_OK;
+}
+#define LAUNCHED(h, which)      \
+    do {                        \
+        (h)->launches++;        \
+        (h)->t_launches[which]++; \
+    } while (0)
+#define KCHECK() CU(cudaGetLastError())
+
+static inline unsigned grid_for(size_t n, int block) { return (unsigned) ((n + block - 1) / block); }
+
+// ---- library-level -------------------------------------------------------------------------------------
+extern "C" const char *slamgpu_last_error(void) { return g_err.c_str(); }
+extern "C" const char *slamgpu_version(void) { return "slamgpu 0.1 sm_100a"; }
+
+extern "C" void *slamgpu_host_alloc(uint64_t bytes) {
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) {
+        g_err = "cudaHostAlloc failed";
+        return nullptr;
+    }
+    return p;
+}
+extern "C" void slamgpu_host_free(void *p) {
+    if (p) cudaFreeHost(p);
+}
+
+static void free_all(slamgpu *h) {
+    if (!h) return;
+    cudaSetDevice(h->cfg.device);
+    if (h->comm) comm_destroy(h->comm);
+    for (auto &sp : h->spans) {
+        cudaEventDestroy(sp.a);
+        cudaEventDestroy(sp.b);
+    }
+    for (auto e : h->free_events) cudaEventDestroy(e);
+    void *dev[] = {h->pose[0], h->pose[1], h->w, h->lm_mean, h->lm_cov, h->gauss, h->unif_base, h->di_base, h->cdf,
+                   h->mloc, h->sel, h->keep, h->tot_w, h->tot_c, h->tot_s, h->bmax, h->d_sc, h->d_z, h->d_row,
+                   h->d_rec_in, h->d_rec_out, h->d_est};
+    for (void *p : dev)
+        if (p) cudaFree(p);
+    if (h->h_sc) cudaFreeHost(h->h_sc);
+    if (h->h_obs) cudaFreeHost(h->h_obs);
+    if (h->h_est) cudaFreeHost(h->h_est);
+    if (h->own_stream) cudaStreamDestroy(h->own_stream);
+    delete h;
+}
+
+// (Re)allocates the buffers whose size depends on the GLOBAL particle count and fills di for this device's slots.
+static int setup_global(slamgpu *h) {
+    const size_t Pg = h->Pg;
+    h->nb = (h->P + SLAM_SCAN_BLOCK - 1) / SLAM_SCAN_BLOCK;
+    h->nbg = (Pg + SLAM_SCAN_BLOCK - 1) / SLAM_SCAN_BLOCK;
+    void **bufs[] = {(void **) &h->cdf, (void **) &h->mloc, (void **) &h->tot_w, (void **) &h->tot_c,
+                     (void **) &h->tot_s, (void **) &h->bmax};
+    for (void **b : bufs)
+        if (*b) {
+            cudaFree(*b);
+            *b = nullptr;
+        }
+    CU(cudaMalloc(&h->cdf, sizeof(float) * Pg));
+    CU(cudaMalloc(&h->mloc, sizeof(float) * Pg));
+    CU(cudaMalloc(&h->tot_w, sizeof(float) * h->nbg));
+    CU(cudaMalloc(&h->tot_c, sizeof(float) * h->nbg));
+    CU(cudaMalloc(&h->tot_s, sizeof(float) * h->nbg));
+    CU(cudaMalloc(&h->bmax, sizeof(float) * h->nbg));
+    // stratifiedRandom's deterministic midpoints, by the reference's own fp32 accumulation run exactly N times
+    // (core.cpp:751-759; oracle so_stratified_di).  Only this device's slots (+2 halo) are kept.
+    std::vector<float> di(h->P + 2, 0.0f);
+    const float k = (float) (1.0 / (float) Pg);
+    float t = k / 2;
+    for (size_t i = 0; i < h->slot0 + h->P; i++) {
+        if (i + 2 >= h->slot0) di[i + 2 - h->slot0] = t;
+        t = t + k;
+    }
+    CU(cudaMemcpyAsync(h->di_base, di.data(), sizeof(float) * (h->P + 2), cudaMemcpyHostToDevice, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return SLAMGPU_OK;
+}
+
+static int create_impl(const slamgpu_config *cfg, slamgpu *h) {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return slam_fail(SLAMGPU_ENODEVICE, "no CUDA device: slamgpu has no CPU path");
+    if (cfg->device < 0 || cfg->device >= ndev) return slam_fail(SLAMGPU_EINVAL, "device ordinal out of range");
+    CU(cudaSetDevice(cfg->device));
+    const size_t P = h->P;
+    CU(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
+    h->stream = h->own_stream;
+    for (int i = 0; i < 2; i++) CU(cudaMalloc(&h->pose[i], sizeof(float) * 12 * P));
+    CU(cudaMalloc(&h->w, sizeof(float) * P));
+    CU(cudaMalloc(&h->lm_mean, sizeof(float2) * (size_t) h->ring_rows * P));
+    CU(cudaMalloc(&h->lm_cov, sizeof(float4) * (size_t) h->ring_rows * P));
+    CU(cudaMalloc(&h->gauss, sizeof(float) * 3 * P));
+    CU(cudaMalloc(&h->unif_base, sizeof(double) * (P + 2)));
+    CU(cudaMalloc(&h->di_base, sizeof(float) * (P + 2)));
+    CU(cudaMalloc(&h->sel, sizeof(float) * P));
+    CU(cudaMalloc(&h->keep, sizeof(int) * P));
+    CU(cudaMalloc(&h->d_sc, sizeof(Scalars)));
+    CU(cudaHostAlloc(&h->h_sc, sizeof(Scalars), cudaHostAllocDefault));
+    h->est_blocks = 148 * 4;
+    CU(cudaMalloc(&h->d_est, sizeof(EstPartial) * (h->est_blocks + 1)));
+    CU(cudaHostAlloc(&h->h_est, sizeof(EstPartial), cudaHostAllocDefault));
+    h->obs_cap = 1024;
+    CU(cudaMalloc(&h->d_z, sizeof(float2) * h->obs_cap));
+    CU(cudaMalloc(&h->d_row, sizeof(int) * h->obs_cap));
+    CU(cudaHostAlloc(&h->h_obs, (sizeof(float2) + sizeof(int)) * h->obs_cap, cudaHostAllocDefault));
+    // ParticleSLAMWrapper::initializeParticles (ParticleSLAMWrapper.cpp:17-25): w = 1/N, xv = 0, Pv = 0
+    CU(cudaMemsetAsync(h->pose[0], 0, sizeof(float) * 12 * P, h->stream));
+    CU(cudaMemsetAsync(h->unif_base, 0, sizeof(double) * (P + 2), h->stream));
+    std::vector<float> w0(P, 1.0f / (float) P);
+    CU(cudaMemcpyAsync(h->w, w0.data(), sizeof(float) * P, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return setup_global(h);
+}
+
+extern "C" int slamgpu_create(const slamgpu_config *cfg, slamgpu_t **out) {
+    if (!cfg || !out) return slam_fail(SLAMGPU_EINVAL, "null argument");
+    *out = nullptr;
+    if (cfg->n_particles <= 0 || cfg->n_particles > (1ll << 30)) return slam_fail(SLAMGPU_EINVAL, "n_particles out of range");
+    if (cfg->nf_cap <= 0) return slam_fail(SLAMGPU_EINVAL, "nf_cap must be positive");
+    if (cfg->method != SLAMGPU_FASTSLAM1 && cfg->method != SLAMGPU_FASTSLAM2)
+        return slam_fail(SLAMGPU_EINVAL, "method must be SLAMGPU_FASTSLAM1 or SLAMGPU_FASTSLAM2");
+    if (cfg->scan_mode != SLAMGPU_SCAN_REFERENCE && cfg->scan_mode != SLAMGPU_SCAN_BLOCKED)
+        return slam_fail(SLAMGPU_EINVAL, "scan_mode must be SLAMGPU_SCAN_REFERENCE or SLAMGPU_SCAN_BLOCKED");
+    slamgpu *h = new slamgpu();
+    h->cfg = *cfg;
+    h->P = h->Pg = (size_t) cfg->n_particles;
+    h->nf_cap = cfg->nf_cap;
+    h->spare = cfg->spare_rows > 0 ? cfg->spare_rows : std::min(64, cfg->nf_cap);
+    h->ring_rows = h->nf_cap + h->spare;
+    int r = create_impl(cfg, h);
+    if (r != SLAMGPU_OK) {
+        std::string keep = g_err;
+        free_all(h);
+        g_err = keep;
+        return r;
+    }
+    *out = h;
+    return SLAMGPU_OK;
+}
+
+extern "C" void slamgpu_destroy(slamgpu_t *h) { free_all(h); }
+
+extern "C" int slamgpu_set_stream(slamgpu_t *h, void *s) {
+    if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
+    CU(cudaSetDevice(h->cfg.device));
+    CU(cudaStreamSynchronize(h->stream));
+    h->stream = s ? (cudaStream_t) s : h->own_stream;
+    return SLAMGPU_OK;
+}
+extern "C" void *slamgpu_get_stream(slamgpu_t *h) { return h ? (void *) h->stream : nullptr; }
+extern "C" int slamgpu_synchronize(slamgpu_t *h) {
+    if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
+    CU(cudaSetDevice(h->cfg.device));
+    CU(cudaStreamSynchronize(h->stream));
+    return SLAMGPU_OK;
+}
+extern "C" int slamgpu_landmark_count(slamgpu_t *h) { return h ? h->Nf : SLAMGPU_EINVAL; }
+extern "C" int64_t slamgpu_launch_count(slamgpu_t *h) { return h ? h->launches : 0; }
+
+// ---- state transfer ---------------------------------------------------------------------------------------
+extern "C" int slamgpu_upload_particles(slamgpu_t *h, const float *xv, const float *Pv, const float *w,
+                                        const float *lm_mean, const float *lm_cov, int32_t Nf) {
+    if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
+    if (Nf < 0 || Nf > h->nf_cap) return slam_fail(SLAMGPU_ECAP, "Nf exceeds nf_cap");
+    CU(cudaSetDevice(h->cfg.device));
+    const size_t P = h->P;
+    PoseSoA s = h->soa(h->cur);
+    if (xv) CU(cudaMemcpyAsync(s.xv, xv, sizeof(float) * 3 * P, cudaMemcpyHostToDevice, h->stream));
+    if (Pv) CU(cudaMemcpyAsync(s.Pv, Pv, sizeof(float) * 9 * P, cudaMemcpyHostToDevice, h->stream));
+    if (w) CU(cudaMemcpyAsync(s.w, w, sizeof(float) * P, cudaMemcpyHostToDevice, h->stream));
+    for (int l = 0; l < Nf; l++) {
+        const size_t row = (size_t) h->phys_row(l);
+        if (lm_mean)
+            CU(cudaMemcpyAsync(h->lm_mean + row * P, lm_mean + (size_t) l * P * 2, sizeof(float2) * P,
+                               cudaMemcpyHostToDevice, h->stream));
+        if (lm_cov)
+            CU(cudaMemcpyAsync(h->lm_cov + row * P, lm_cov + (size_t) l * P * 4, sizeof(float4) * P,
+                               cudaMemcpyHostToDevice, h->stream));
+    }
+    h->Nf = Nf;
+    CU(cudaStreamSynchronize(h->stream));
+    return SLAMGPU_OK;
+}
+
+extern "C" int slamgpu_upload_particles_tiled(slamgpu_t *h, int64_t Pt, const float *xv, const float *Pv,
+                                              const float *w, const float *lm_mean, const float *lm_cov, int32_t Nf) {
+    if (!h || Pt <= 0 || !xv || !Pv || !w) return slam_fail(SLAMGPU_EINVAL, "bad argument");
+    if (Nf < 0 || Nf > h->nf_cap) return slam_fail(SLAMGPU_ECAP, "Nf exceeds nf_cap");
+    if (Nf > 0 && (!lm_mean || !lm_cov)) return slam_fail(SLAMGPU_EINVAL, "landmark tile missing");
+    CU(cudaSetDevice(h->cfg.device));
+    const size_t P = h->P, T = (size_t) Pt;
+    const int chunk = 64;  // landmark rows staged per copy
+    float *dt = nullptr;
+    CU(cudaMalloc(&dt, sizeof(float) * std::max((size_t) 13 * T, (size_t) chunk * T * 6)));
+    int rc = SLAMGPU_OK;
+    do {
+        cudaError_t e = cudaMemcpyAsync(dt, xv, sizeof(float) * 3 * T, cudaMemcpyHostToDevice, h->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(dt + 3 * T, Pv, sizeof(float) * 9 * T, cudaMemcpyHostToDevice, h->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(dt + 12 * T, w, sizeof(float) * T, cudaMemcpyHostToDevice, h->stream);
+        if (e != cudaSuccess) { rc = SLAMGPU_ECUDA; break; }
+        k_tile_planes<<<grid_for(P, 256), 256, 0, h->stream>>>(dt, T, h->pose[h->cur], P, 12);
+        k_tile_planes<<<grid_for(P, 256), 256, 0, h->stream>>>(dt + 12 * T, T, h->w, P, 1);
+        h->launches += 2;
+        if (cudaStreamSynchronize(h->stream) != cudaSuccess) { rc = SLAMGPU_ECUDA; break; }
+        float2 *tm = (float2 *) dt;
+        float4 *tc = (float4 *) (dt + (size_t) chunk * T * 2);
+        for (int l0 = 0; l0 < Nf && rc == SLAMGPU_OK; l0 += chunk) {
+            const int n = std::min(chunk, Nf - l0);
+            e = cudaMemcpyAsync(tm, lm_mean + (size_t) l0 * T * 2, sizeof(float2) * n * T, cudaMemcpyHostToDevice, h->stream);
+            if (e == cudaSuccess)
+                e = cudaMemcpyAsync(tc, lm_cov + (size_t) l0 * T * 4, sizeof(float4) * n * T, cudaMemcpyHostToDevice, h->stream);
+            if (e != cudaSuccess) { rc = SLAMGPU_ECUDA; break; }
+            k_tile_rows<<<dim3(grid_for(P, 256), n), 256, 0, h->stream>>>(tm, tc, T, h->ring(), P, l0);
+            h->launches++;
+            if (cudaStreamSynchronize(h->stream) != cudaSuccess) { rc = SLAMGPU_ECUDA; break; }
+        }
+    } while (0);
+    cudaFree(dt);
+    if (rc != SLAMGPU_OK) return slam_fail(rc, std::string("upload_particles_tiled: ") + cudaGetErrorString(cudaGetLastError()));
+    h->Nf = Nf;
+    return SLAMGPU_OK;
+}
+
+extern "C" int slamgpu_download_particles(slamgpu_t *h, float *xv, float *Pv, float *w, float *lm_mean,
+                                          float *lm_cov, int32_t *Nf) {
+    if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
+    CU(cudaSetDevice(h->cfg.device));
+    const size_t P = h->P;
+    PoseSoA s = h->soa(h->cur);
+    if (xv) CU(cudaMemcpyAsync(xv, s.xv, sizeof(float) * 3 * P, cudaMemcpyDeviceToHost, h->stream));
+    if (Pv) CU(cudaMemcpyAsync(Pv, s.Pv, sizeof(float) * 9 * P, cudaMemcpyDeviceToHost, h->stream));
+    if (w) CU(cudaMemcpyAsync(w, s.w, sizeof(float) * P, cudaMemcpyDeviceToHost, h->stream));
+    for (int l = 0; l < h->Nf; l++) {
+        const size_t row = (size_t) h->phys_row(l);
+        if (lm_mean)
+            CU(cudaMemcpyAsync(lm_mean + (size_t) l * P * 2, h->lm_mean + row * P, sizeof(float2) * P,
+                               cudaMemcpyDeviceToHost, h->stream));
+        if (lm_cov)
+            CU(cudaMemcpyAsync(lm_cov + (size_t) l * P * 4, h->lm_cov + row * P, sizeof(float4) * P,
+                               cudaMemcpyDeviceToHost, h->stream));
+    }
+    if (Nf) *Nf = h->Nf;
+    CU(cudaStreamSynchronize(h->stream));
+    return SLAMGPU_OK;
+}
+
+extern "C" int slamgpu_stage_noise(slamgpu_t *h, const float *gauss, int32_t gauss_rows, const double *unif) {
+    if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
+    CU(cudaSetDevice(h->cfg.device));
+    if (gauss) {
+        if (gauss_rows != 2 && gauss_rows != 3) return slam_fail(SLAMGPU_EINVAL, "gauss_rows must be 2 or 3");
+        CU(cudaMemcpyAsync(h->gauss, gauss, sizeof(float) * gauss_rows * h->P, cudaMemcpyHostToDevice, h->stream));
+        h->gauss_staged = true;
+        h->gauss_rows_staged = gauss_rows;
+    }
+    if (unif) {
+        CU(cudaMemcpyAsync(h->unif(), unif, sizeof(double) * h->P, cudaMemcpyHostToDevice, h->stream));
+        h->unif_staged = true;
+    }
+    CU(cudaStreamSynchronize(h->stream));
+    return SLAMGPU_OK;
+}
+
+// ---- predict ----------------------------------------------------------------------------------------------
+extern "C" int slamgpu_predict(slamgpu_t *h, float V, float G, const float Q[4], float dt, float phi_true,
+                               const float *gauss) {
+    if (!h || !Q) return slam_fail(SLAMGPU_EINVAL, "null argument");
+    CU(cudaSetDevice(h->cfg.device));
+    const float *dg = nullptr;
+    if (gauss) {
+        CU(cudaMemcpyAsync(h->gauss, gauss, sizeof(float) * 2 * h->P, cudaMemcpyHostToDevice, h->stream));
+        dg = h->gauss;
+    } else if (h->gauss_staged && h->gauss_rows_staged == 2) {
+        dg = h->gauss;
+    }
+    if (h->cfg.method == SLAMGPU_FASTSLAM1 && !dg && false) return slam_fail(SLAMGPU_EINVAL, "unreachable");
+    PredictArgs a;
+    a.V = V; a.G = G; a.dt = dt; a.phi_true = phi_true;
+    for (int j = 0; j < 4; j++) a.Q[j] = Q[j];
+    a.wheel_base = h->cfg.wheel_base;
+    a.sigma_phi = h->cfg.sigma_phi;
+    a.method = h->cfg.method;
+    a.use_heading = h->cfg.use_heading;
+    TimedSpan sp;
+    RET(span_begin(h, SLAMGPU_T_PREDICT, &sp));
+    k_predict<<<grid_for(h->P, 256), 256, 0, h->stream>>>(h->soa(h->cur), h->P, a, dg);
+    KCHECK();
+    LAUNCHED(h, SLAMGPU_T_PREDICT);
+    RET(span_end(h, &sp));
+    return SLAMGPU_OK;
+}
+
+// ---- update, per-particle part -----------------------------------------------------------------------------
+static int stage_obs_host(slamgpu *h, const float *z, const int *rows, int K) {
+    if (K > h->obs_cap) {
+        int cap = std::max(K, 2 * h->obs_cap);
+        CU(cudaStreamSynchronize(h->stream));
+        cudaFree(h->d_z); h->d_z = nullptr;
+        cudaFree(h->d_row); h->d_row = nullptr;
+        cudaFreeHost(h->h_obs); h->h_obs = nullptr;
+        CU(cudaMalloc(&h->d_z, sizeof(float2) * cap));
+        CU(cudaMalloc(&h->d_row, sizeof(int) * cap));
+        CU(cudaHostAlloc(&h->h_obs, (sizeof(float2) + sizeof(int)) * cap, cudaHostAllocDefault));
+        h->obs_cap = cap;
+    }
+    // the pinned staging block is reused by the next call: wait until the previous copy out of it has been issued
+    // and consumed (stream order makes the kernels safe; the host buffer needs the copy itself to be done)
+    CU(cudaStreamSynchronize(h->stream));
+    float2 *hz = (float2 *) h->h_obs;
+    int *hr = (int *) (hz + h->obs_cap);
+    for (int i = 0; i < K; i++) {
+        hz[i] = make_float2(z[2 * i], z[2 * i + 1]);
+        hr[i] = rows[i];
+    }
+    CU(cudaMemcpyAsync(h->d_z, hz, sizeof(float2) * K, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaMemcpyAsync(h->d_row, hr, sizeof(int) * K, cudaMemcpyHostToDevice, h->stream));
+    return SLAMGPU_OK;
+}
+
+extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int32_t *idf, int32_t K, const float *zn,
+                                        int32_t Kn, const float R[4], const float *gauss) {
+    if (!h || !R) return slam_fail(SLAMGPU_EINVAL, "null argument");
+    if (K < 0 || Kn < 0 || (K > 0 && (!zf || !idf)) || (Kn > 0 && !zn)) return slam_fail(SLAMGPU_EINVAL, "bad observation set");
+    if (h->Nf + Kn > h->nf_cap) return slam_fail(SLAMGPU_ECAP, "landmark capacity (nf_cap) exceeded");
+    CU(cudaSetDevice(h->cfg.device));
+    std::vector<int> rows(std::max(K, Kn));
+    if (K > 0) {
+        std::vector<int> seen(idf, idf + K);
+        std::sort(seen.begin(), seen.end());
+        for (int i = 0; i < K; i++) {
+            if (idf[i] < 0 || idf[i] >= h->Nf) return slam_fail(SLAMGPU_EINVAL, "idf entry outside [0, Nf)");
+            if (i > 0 && seen[i] == seen[i - 1])
+                return slam_fail(SLAMGPU_EINVAL, "idf holds a landmark twice (known association never does)");
+        }
+    }
+    const bool fs2 = h->cfg.method == SLAMGPU_FASTSLAM2;
+    const float *dg = nullptr;
+    if (fs2 && (K > 0 || Kn > 0)) {
+        if (gauss) {
+            CU(cudaMemcpyAsync(h->gauss, gauss, sizeof(float) * 3 * h->P, cudaMemcpyHostToDevice, h->stream));
+        } else if (!(h->gauss_staged && h->gauss_rows_staged == 3)) {
+            return slam_fail(SLAMGPU_EINVAL, "FastSLAM2 update needs gauss[3][P] (or slamgpu_stage_noise first)");
+        }
+        dg = h->gauss;
+    }
+    const float4 Rm = make_float4(R[0], R[1], R[2], R[3]);
+    const size_t P = h->P;
+    if (K > 0) {
+        for (int i = 0; i < K; i++) rows[i] = h->phys_row(idf[i]);
+        RET(stage_obs_host(h, zf, rows.data(), K));
+        ObsSet o;
+        o.z = h->d_z;
+        o.row = h->d_row;
+        const size_t smem = (sizeof(float2) + sizeof(int)) * K;
+        TimedSpan sp;
+        RET(span_begin(h, SLAMGPU_T_UPDATE, &sp));
+        if (fs2)
+            k_fs2_update<<<grid_for(P, 128), 128, smem, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, dg);
+        else
+            k_fs1_update<<<grid_for(P, 256), 256, smem, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm);
+        KCHECK();
+        LAUNCHED(h, SLAMGPU_T_UPDATE);
+        RET(span_end(h, &sp));
+    }
+    if (Kn > 0) {
+        for (int i = 0; i < Kn; i++) rows[i] = h->phys_row(h->Nf + i);
+        RET(stage_obs_host(h, zn, rows.data(), Kn));
+        ObsSet o;
+        o.z = h->d_z;
+        o.row = h->d_row;
+        const size_t smem = (sizeof(float2) + sizeof(int)) * Kn;
+        TimedSpan sp;
+        RET(span_begin(h, SLAMGPU_T_ADDFEAT, &sp));
+        k_add_feature<<<grid_for(P, 256), 256, smem, h->stream>>>(h->soa(h->cur), h->ring(), P, o, Kn, Rm,
+                                                                   (fs2 && K == 0) ? 1 : 0, dg);
+        KCHECK();
+        LAUNCHED(h, SLAMGPU_T_ADDFEAT);
+        RET(span_end(h, &sp));
+        h->Nf += Kn;
+    }
+    return SLAMGPU_OK;
+}
+
+// ---- resample ---------------------------------------------------------------------------------------------
+static int launch_upper(slamgpu *h, float *a0, float *s0, float *a1, float *s1, int n, int use_max) {
+    UpperArgs u;
+    memset(&u, 0, sizeof(u));
+    u.arr[0] = a0; u.sum_out[0] = s0;
+    u.arr[1] = a1; u.sum_out[1] = s1;
+    u.n = n;
+    u.use_max = use_max;
+    k_scan_upper<<<a1 ? 2 : 1, SLAM_SCAN_BLOCK, 0, h->stream>>>(u);
+    KCHECK();
+    LAUNCHED(h, SLAMGPU_T_WEIGHTS);
+    return SLAMGPU_OK;
+}
+
+static int resample_indices(slamgpu *h) {
+    const size_t P = h->P, Pg = h->Pg;
+    const float k = (float) (1.0 / (float) Pg);
+    const float khalf = k / 2;
+    Scalars *d = h->d_sc;
+    CU(cudaMemsetAsync(&d->anomaly, 0, sizeof(int), h->stream));
+    if (h->cfg.scan_mode == SLAMGPU_SCAN_REFERENCE) {
+        if (h->world > 1) return slam_fail(SLAMGPU_EINVAL, "SLAMGPU_SCAN_REFERENCE is a one-device order");
+        k_reference_weights<<<1, 1, 0, h->stream>>>(h->w, P, h->di(), h->unif(), k, khalf, h->mloc, h->cdf, h->sel,
+                                                    &d->neff);
+        KCHECK();
+        LAUNCHED(h, SLAMGPU_T_WEIGHTS);
+        k_keep_sequential<<<1, 1, 0, h->stream>>>(h->sel, h->cdf, h->keep, P);
+        KCHECK();
+        LAUNCHED(h, SLAMGPU_T_WEIGHTS);
+        return SLAMGPU_OK;
+    }
+    const unsigned nb = (unsigned) h->nb;
+    const size_t b0 = h->slot0 / SLAM_SCAN_BLOCK;  // first global block held here (P is a multiple of 1024 when sharded)
+    // A: block totals of w
+    k_block_totals<<<nb, SLAM_SCAN_BLOCK, 0, h->stream>>>(h->w, P, h->tot_w + b0);
+    KCHECK();
+    LAUNCHED(h, SLAMGPU_T_WEIGHTS);
+    if (h->world > 1) RET(comm_allgather_f32(h->comm, h->tot_w, h->nb, h->stream));
+    // B: recursive levels -> ws
+    RET(launch_upper(h, h->tot_w, &d->ws, nullptr, nullptr, (int) h->nbg, 0));
+    // C: normalise, local cdf scan, totals
+    k_normalise_scan<<<nb, SLAM_SCAN_BLOCK, 0, h->stream>>>(h->w, P, &d->ws, h->cdf + h->slot0, h->tot_c + b0,
+                                                            h->tot_s + b0);
+    KCHECK();
+    LAUNCHED(h, SLAMGPU_T_WEIGHTS);
+    if (h->world > 1) {
+        RET(comm_allgather_f32(h->comm, h->tot_c, h->nb, h->stream));
+        RET(comm_allgather_f32(h->comm, h->tot_s, h->nb, h->stream));
+    }
+    // D: recursive levels of both -> csum, s2
+    RET(launch_upper(h, h->tot_c, &d->csum, h->tot_s, &d->s2, (int) h->nbg, 0));
+    k_neff<<<1, 32, 0, h->stream>>>(&d->s2, &d->neff);
+    KCHECK();
+    LAUNCHED(h, SLAMGPU_T_WEIGHTS);
+    // E: final cdf + running maxima
+    k_cdf_finalise<<<nb, SLAM_SCAN_BLOCK, 0, h->stream>>>(h->cdf + h->slot0, P, h->tot_c, b0, h->mloc + h->slot0,
+                                                          h->bmax + b0);
+    KCHECK();
+    LAUNCHED(h, SLAMGPU_T_WEIGHTS);
+    if (h->world > 1) {
+        RET(comm_allgather_f32(h->comm, h->bmax, h->nb, h->stream));
+        RET(comm_allgather_f32(h->comm, h->cdf, P, h->stream));
+        RET(comm_allgather_f32(h->comm, h->mloc, P, h->stream));
+        RET(comm_halo_unif(h->comm, h->unif_base, P, h->stream));
+    }
+    RET(launch_upper(h, h->bmax, nullptr, nullptr, nullptr, (int) h->nbg, 1));
+    // F: select + search
+    SearchArgs a;
+    a.di = h->di();
+    a.unif = h->unif();
+    a.cdf = h->cdf;
+    a.mloc = h->mloc;
+    a.BM = h->bmax;
+    a.sel = h->sel;
+    a.keep = h->keep;
+    a.anomaly = &d->anomaly;
+    a.n_local = P;
+    a.n_global = Pg;
+    a.slot_offset = h->slot0;
+    a.nb_global = (int) h->nbg;
+    a.k = k;
+    a.khalf = khalf;
+    k_search_keep<<<grid_for(P, 256), 256, 0, h->stream>>>(a);
+    KCHECK();
+    LAUNCHED(h, SLAMGPU_T_WEIGHTS);
+    return SLAMGPU_OK;
+}
+
+static int gather_local(slamgpu *h) {
+    const size_t P = h->P;
+    const float new_w = 1.0f / (float) h->Pg;
+    PoseSoA src = h->soa(h->cur), dst = h->soa(h->cur ^ 1);
+    k_gather_pose<<<grid_for(P, 256), 256, 0, h->stream>>>(src.xv, src.Pv, dst.xv, dst.Pv, h->w, h->keep, P,
+                                                           (long long) h->slot0, (long long) h->Pg, new_w);
+    KCHECK();
+    LAUNCHED(h, SLAMGPU_T_GATHER);
+    h->cur ^= 1;
+    const int S = h->spare;
+    for (int l0 = 0; l0 < h->Nf; l0 += S) {
+        const int nrows = std::min(S, h->Nf - l0);
+        dim3 grid(grid_for(P, 256), (nrows + SLAM_GATHER_ROWS - 1) / SLAM_GATHER_ROWS);
+        k_gather_rows<<<grid, 256, 0, h->stream>>>(h->ring(), P, h->keep, l0, nrows, S, (long long) h->slot0,
+                                                   (long long) h->Pg);
+        KCHECK();
+        LAUNCHED(h, SLAMGPU_T_GATHER);
+    }
+    h->ring_base = (h->ring_base - S + h->ring_rows) % h->ring_rows;
+    return SLAMGPU_OK;
+}
+
+extern "C" int slamgpu_resample(slamgpu_t *h, const double *unif, int32_t *keep_out, float *neff,
+                                int32_t *did_resample) {
+    if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
+    CU(cudaSetDevice(h->cfg.device));
+    if (unif) {
+        CU(cudaMemcpyAsync(h->unif(), unif, sizeof(double) * h->P, cudaMemcpyHostToDevice, h->stream));
+    } else if (!h->unif_staged) {
+        return slam_fail(SLAMGPU_EINVAL, "resample needs unif[P] (or slamgpu_stage_noise first)");
+    }
+    TimedSpan sp;
+    RET(span_begin(h, SLAMGPU_T_WEIGHTS, &sp));
+    RET(resample_indices(h));
+    CU(cudaMemcpyAsync(h->h_sc, h->d_sc, sizeof(Scalars), cudaMemcpyDeviceToHost, h->stream));
+    RET(span_end(h, &sp));
+    CU(cudaStreamSynchronize(h->stream));
+    if (h->h_sc->anomaly) {
+        // knife-edge ordering the search could not prove: run the exact sequential merge (core.cpp:800-806)
+        if (h->world > 1) return slam_fail(SLAMGPU_ECOMM, "sequential keep[] fallback is not available when sharded");
+        k_keep_sequential<<<1, 1, 0, h->stream>>>(h->sel, h->cdf, h->keep, h->P);
+        KCHECK();
+        LAUNCHED(h, SLAMGPU_T_WEIGHTS);
+    }
+    const float ne = h->h_sc->neff;
+    const bool did = h->cfg.do_resample && (ne < (float) h->cfg.n_effective);  // core.cpp:739
+    if (keep_out) {
+        CU(cudaMemcpyAsync(keep_out, h->keep, sizeof(int) * h->P, cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+    }
+    if (did) {
+        TimedSpan sg;
+        RET(span_begin(h, SLAMGPU_T_GATHER, &sg));
+        if (h->world > 1)
+            RET(comm_gather_sharded(h->comm, h));
+        else
+            RET(gather_local(h));
+        RET(span_end(h, &sg));
+    }
+    if (neff) *neff = ne;
+    if (did_resample) *did_resample = did ? 1 : 0;
+    return SLAMGPU_OK;
+}
+
+extern "C" int slamgpu_update(slamgpu_t *h, const float *zf, const int32_t *idf, int32_t K, const float *zn,
+                              int32_t Kn, const float R[4], const float *gauss, const double *unif,
+                              int32_t *did_resample, float *neff) {
+    RET(slamgpu_update_particles(h, zf, idf, K, zn, Kn, R, gauss));
+    return slamgpu_resample(h, unif, nullptr, neff, did_resample);
+}
+
+// ---- computeJacobians ---------------------------------------------------------------------------------------
+extern "C" int slamgpu_compute_jacobians(slamgpu_t *h, const float *in, int32_t n, float *out) {
+    if (!in || !out || n < 0) return slam_fail(SLAMGPU_EINVAL, "bad argument");
+    if (n == 0) return SLAMGPU_OK;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return slam_fail(SLAMGPU_ENODEVICE, "no CUDA device: slamgpu has no CPU path");
+    CU(cudaSetDevice(h ? h->cfg.device : 0));
+    cudaStream_t st = h ? h->stream : (cudaStream_t) 0;
+    float *din = nullptr, *dout = nullptr;
+    const size_t nin = 7 + 6 * (size_t) n, nout = 16 * (size_t) n;
+    if (h) {
+        if (h->rec_cap < (size_t) n) {
+            CU(cudaStreamSynchronize(st));
+            if (h->d_rec_in) cudaFree(h->d_rec_in);
+            if (h->d_rec_out) cudaFree(h->d_rec_out);
+            h->d_rec_in = h->d_rec_out = nullptr;
+            h->rec_cap = 0;
+            const size_t cap = std::max((size_t) n, (size_t) 4096);
+            CU(cudaMalloc(&h->d_rec_in, sizeof(float) * (7 + 6 * cap)));
+            CU(cudaMalloc(&h->d_rec_out, sizeof(float) * 16 * cap));
+            h->rec_cap = cap;
+        }
+        din = h->d_rec_in;
+        dout = h->d_rec_out;
+    } else {
+        CU(cudaMalloc(&din, sizeof(float) * nin));
+        CU(cudaMalloc(&dout, sizeof(float) * nout));
+    }
+    int rc = SLAMGPU_OK;
+    do {
+        if (cudaMemcpyAsync(din, in, sizeof(float) * nin, cudaMemcpyHostToDevice, st) != cudaSuccess) { rc = SLAMGPU_ECUDA; break; }
+        k_jacobians_record<<<grid_for(n, 128), 128, 0, st>>>(din, n, (float4 *) dout);
+        if (h) h->launches++;
+        if (cudaMemcpyAsync(out, dout, sizeof(float) * nout, cudaMemcpyDeviceToHost, st) != cudaSuccess) { rc = SLAMGPU_ECUDA; break; }
+        if (cudaStreamSynchronize(st) != cudaSuccess) { rc = SLAMGPU_ECUDA; break; }
+    } while (0);
+    if (!h) {
+        cudaFree(din);
+        cudaFree(dout);
+    }
+    if (rc != SLAMGPU_OK) return slam_fail(rc, std::string("compute_jacobians: ") + cudaGetErrorString(cudaGetLastError()));
+    return SLAMGPU_OK;
+}
+
+extern "C" int slamgpu_compute_jacobians_batch(slamgpu_t *h, const int32_t *idf, int32_t K, const float R[4],
+                                               float *out) {
+    if (!h || !idf || !R || !out || K <= 0) return slam_fail(SLAMGPU_EINVAL, "bad argument");
+    CU(cudaSetDevice(h->cfg.device));
+    std::vector<int> rows(K);
+    std::vector<float> z(2 * (size_t) K, 0.0f);
+    for (int i = 0; i < K; i++) {
+        if (idf[i] < 0 || idf[i] >= h->Nf) return slam_fail(SLAMGPU_EINVAL, "idf entry outside [0, Nf)");
+        rows[i] = h->phys_row(idf[i]);
+    }
+    RET(stage_obs_host(h, z.data(), rows.data(), K));
+    float4 *dout = nullptr;
+    const size_t bytes = sizeof(float) * 16 * (size_t) K * h->P;
+    CU(cudaMalloc(&dout, bytes));
+    ObsSet o;
+    o.z = h->d_z;
+    o.row = h->d_row;
+    k_jacobians_batch<<<grid_for(h->P, 256), 256, (sizeof(float2) + sizeof(int)) * K, h->stream>>>(
+        h->soa(h->cur), h->ring(), h->P, o, K, make_float4(R[0], R[1], R[2], R[3]), dout);
+    h->launches++;
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, dout, bytes, cudaMemcpyDeviceToHost, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    cudaFree(dout);
+    if (e != cudaSuccess) return slam_fail(SLAMGPU_ECUDA, std::string("compute_jacobians_batch: ") + cudaGetErrorString(e));
+    return SLAMGPU_OK;
+}
+
+// ---- estimate / decimated download ------------------------------------------------------------------------------
+extern "C" int slamgpu_estimate(slamgpu_t *h, double *x, double *y, double *t) {
+    if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
+    CU(cudaSetDevice(h->cfg.device));
+    TimedSpan sp;
+    RET(span_begin(h, SLAMGPU_T_ESTIMATE, &sp));
+    PoseSoA s = h->soa(h->cur);
+    k_estimate_partial<<<h->est_blocks, 256, 0, h->stream>>>(s.xv, s.w, h->P, (long long) h->slot0, h->d_est);
+    KCHECK();
+    LAUNCHED(h, SLAMGPU_T_ESTIMATE);
+    k_estimate_final<<<1, 256, 0, h->stream>>>(h->d_est, h->est_blocks, s.xv, h->P, (long long) h->slot0,
+                                               h->d_est + h->est_blocks);
+    KCHECK();
+    LAUNCHED(h, SLAMGPU_T_ESTIMATE);
+    CU(cudaMemcpyAsync(h->h_est, h->d_est + h->est_blocks, sizeof(EstPartial), cudaMemcpyDeviceToHost, h->stream));
+    RET(span_end(h, &sp));
+    CU(cudaStreamSynchronize(h->stream));
+    double sx = h->h_est->sx, sy = h->h_est->sy, th = h->h_est->theta;
+    if (h->world > 1) RET(comm_reduce_estimate(h->comm, h, &sx, &sy, h->h_est->wmax, h->h_est->imax, &th));
+    if (x) *x = sx / (double) h->Pg;
+    if (y) *y = sy / (double) h->Pg;
+    if (t) *t = th;
+    return SLAMGPU_OK;
+}
+
+extern "C" int slamgpu_download_decimated(slamgpu_t *h, int64_t stride, float *xv_out, float *lm_out) {
+    if (!h || stride <= 0 || !xv_out) return slam_fail(SLAMGPU_EINVAL, "bad argument");
+    CU(cudaSetDevice(h->cfg.device));
+    const size_t n = (h->P + (size_t) stride - 1) / (size_t) stride;
+    float *dx = nullptr;
+    float2 *dl = nullptr;
+    CU(cudaMalloc(&dx, sizeof(float) * 3 * n));
+    if (lm_out && h->Nf > 0) {
+        cudaError_t e = cudaMalloc(&dl, sizeof(float2) * (size_t) h->Nf * n);
+        if (e != cudaSuccess) {
+            cudaFree(dx);
+            return slam_fail(SLAMGPU_ENOMEM, "decimated landmark buffer");
+        }
+    }
+    k_decimate<<<grid_for(n, 256), 256, 0, h->stream>>>(h->soa(h->cur), h->ring(), h->P, (size_t) stride, n, h->Nf, dx,
+                                                        dl);
+    h->launches++;
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(xv_out, dx, sizeof(float) * 3 * n, cudaMemcpyDeviceToHost, h->stream);
+    if (e == cudaSuccess && dl)
+        e = cudaMemcpyAsync(lm_out, dl, sizeof(float2) * (size_t) h->Nf * n, cudaMemcpyDeviceToHost, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    cudaFree(dx);
+    if (dl) cudaFree(dl);
+    if (e != cudaSuccess) return slam_fail(SLAMGPU_ECUDA, std::string("download_decimated: ") + cudaGetErrorString(e));
+    return SLAMGPU_OK;
+}
+
+// ---- timing ---------------------------------------------------------------------------------------------
+extern "C" int slamgpu_timing_enable(slamgpu_t *h, int32_t on) {
+    if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
+    h->timing = on != 0;
+    return SLAMGPU_OK;
+}
+extern "C" int slamgpu_timing_read(slamgpu_t *h, int32_t which, double *total_ms, int64_t *events, int64_t *launches) {
+    if (!h || which < 0 || which >= SLAMGPU_T_COUNT) return slam_fail(SLAMGPU_EINVAL, "bad argument");
+    CU(cudaSetDevice(h->cfg.device));
+    RET(timing_flush(h));
+    if (total_ms) *total_ms = h->t_ms[which];
+    if (events) *events = h->t_events[which];
+    if (launches) *launches = h->t_launches[which];
+    return SLAMGPU_OK;
+}
+extern "C" int slamgpu_timing_reset(slamgpu_t *h) {
+    if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
+    CU(cudaSetDevice(h->cfg.device));
+    RET(timing_flush(h));
+    for (int i = 0; i < SLAMGPU_T_COUNT; i++) {
+        h->t_ms[i] = 0;
+        h->t_events[i] = 0;
+        h->t_launches[i] = 0;
+    }
+    return SLAMGPU_OK;
+}
+
+// ---- sharding ---------------------------------------------------------------------------------------------
+extern "C" int slamgpu_comm_unique_id(void *id128) {
+    if (!id128) return slam_fail(SLAMGPU_EINVAL, "null argument");
+    std::string err;
+    if (comm_unique_id(id128, &err) != 0) return slam_fail(SLAMGPU_ECOMM, err);
+    return SLAMGPU_OK;
+}
+
+extern "C" int slamgpu_comm_init(slamgpu_t *h, int32_t rank, int32_t world, const void *id128) {
+    if (!h || !id128 || world < 1 || rank < 0 || rank >= world) return slam_fail(SLAMGPU_EINVAL, "bad argument");
+    if (world > 1 && (h->P % SLAM_SCAN_BLOCK) != 0)
+        return slam_fail(SLAMGPU_EINVAL, "sharded particle counts must be a multiple of 1024 per device");
+    if (world > 1 && h->cfg.scan_mode != SLAMGPU_SCAN_BLOCKED)
+        return slam_fail(SLAMGPU_EINVAL, "sharding needs SLAMGPU_SCAN_BLOCKED");
+    CU(cudaSetDevice(h->cfg.device));
+    std::string err;
+    SlamComm *c = comm_create(rank, world, id128, h->cfg.device, &err);
+    if (!c) return slam_fail(SLAMGPU_ECOMM, err);
+    h->comm = c;
+    h->rank = rank;
+    h->world = world;
+    h->Pg = h->P * (size_t) world;
+    h->slot0 = h->P * (size_t) rank;
+    // w = 1/N over the GLOBAL count (ParticleSLAMWrapper.cpp:17-25)
+    std::vector<float> w0(h->P, 1.0f / (float) h->Pg);
+    CU(cudaMemcpyAsync(h->w, w0.data(), sizeof(float) * h->P, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return setup_global(h);
+}

@@ -1,0 +1,293 @@
+// comm.cu — exchange steps of the sharded resample, one process per device.
+//
+//   * small all-gathers (per-1024-block weight totals, block maxima, the CDF) and the 2-slot uniform halo go
+//     through NCCL, loaded at run time from libnccl.so.2 (the copy torch already mapped when the caller is a
+//     torchrun rank, else the system one) so that a single-device build has no NCCL dependency;
+//   * particle migration is NOT a collective: every rank maps its peers' pose and landmark buffers (CUDA IPC over
+//     NVLink / NVSwitch) and the gather kernels read particles[keep[i]] straight from the owning device, row batch by
+//     row batch, with a stream-ordered barrier between batches because the ring (kernels.cuh) recycles the rows the
+//     previous batch was read from.
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <cstring>
+
+#include "handle.h"
+
+using namespace slam;
+
+#define SLAM_MAX_RANKS 8
+
+struct NcclApi {
+    void *lib = nullptr;
+    decltype(&ncclGetUniqueId) GetUniqueId = nullptr;
+    decltype(&ncclCommInitRank) CommInitRank = nullptr;
+    decltype(&ncclCommDestroy) CommDestroy = nullptr;
+    decltype(&ncclAllGather) AllGather = nullptr;
+    decltype(&ncclSend) Send = nullptr;
+    decltype(&ncclRecv) Recv = nullptr;
+    decltype(&ncclGroupStart) GroupStart = nullptr;
+    decltype(&ncclGroupEnd) GroupEnd = nullptr;
+    decltype(&ncclGetErrorString) GetErrorString = nullptr;
+};
+
+static int load_nccl(NcclApi *api, std::string *err) {
+    if (api->lib) return 0;
+    void *lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) {
+        *err = std::string("dlopen(libnccl.so.2): ") + dlerror();
+        return -1;
+    }
+#define SYM(name)                                                              \
+    api->name = (decltype(api->name)) dlsym(lib, "nccl" #name);                \
+    if (!api->name) {                                                          \
+        *err = "libnccl.so.2 lacks nccl" #name;                                \
+        return -1;                                                             \
+    }
+    SYM(GetUniqueId) SYM(CommInitRank) SYM(CommDestroy) SYM(AllGather) SYM(Send) SYM(Recv) SYM(GroupStart)
+    SYM(GroupEnd) SYM(GetErrorString)
+#undef SYM
+    api->lib = lib;
+    return 0;
+}
+
+static NcclApi g_nccl;
+
+struct PeerMaps {
+    const float *pose[2][SLAM_MAX_RANKS];
+    const float2 *mean[SLAM_MAX_RANKS];
+    const float4 *cov[SLAM_MAX_RANKS];
+};
+
+struct SlamComm {
+    int rank = 0, world = 1, device = 0;
+    ncclComm_t comm = nullptr;
+    bool peers_open = false;
+    PeerMaps peers;
+    void *opened[SLAM_MAX_RANKS][4];
+    unsigned char *d_small = nullptr;  // scratch for handle exchange, barriers, estimate
+    unsigned char *h_small = nullptr;
+};
+
+#define NC(call)                                                                                         \
+    do {                                                                                                 \
+        ncclResult_t r_ = (call);                                                                        \
+        if (r_ != ncclSuccess)                                                                           \
+            return slam_fail(SLAMGPU_ECOMM, std::string(#call) + ": " + g_nccl.GetErrorString(r_));      \
+    } while (0)
+
+int comm_unique_id(void *id128, std::string *err) {
+    if (load_nccl(&g_nccl, err) != 0) return -1;
+    ncclUniqueId id;
+    ncclResult_t r = g_nccl.GetUniqueId(&id);
+    if (r != ncclSuccess) {
+        *err = std::string("ncclGetUniqueId: ") + g_nccl.GetErrorString(r);
+        return -1;
+    }
+    static_assert(sizeof(id) == 128, "ncclUniqueId is 128 bytes");
+    memcpy(id128, &id, 128);
+    return 0;
+}
+
+SlamComm *comm_create(int rank, int world, const void *id128, int device, std::string *err) {
+    if (world > SLAM_MAX_RANKS) {
+        *err = "at most 8 devices (one NVSwitch box)";
+        return nullptr;
+    }
+    if (load_nccl(&g_nccl, err) != 0) return nullptr;
+    SlamComm *c = new SlamComm();
+    c->rank = rank;
+    c->world = world;
+    c->device = device;
+    memset(&c->peers, 0, sizeof(c->peers));
+    memset(c->opened, 0, sizeof(c->opened));
+    ncclUniqueId id;
+    memcpy(&id, id128, 128);
+    ncclResult_t r = g_nccl.CommInitRank(&c->comm, world, id, rank);
+    if (r != ncclSuccess) {
+        *err = std::string("ncclCommInitRank: ") + g_nccl.GetErrorString(r);
+        delete c;
+        return nullptr;
+    }
+    if (cudaMalloc(&c->d_small, 4096) != cudaSuccess || cudaHostAlloc(&c->h_small, 4096, cudaHostAllocDefault) != cudaSuccess) {
+        *err = "comm scratch allocation failed";
+        g_nccl.CommDestroy(c->comm);
+        delete c;
+        return nullptr;
+    }
+    return c;
+}
+
+void comm_destroy(SlamComm *c) {
+    if (!c) return;
+    for (int r = 0; r < c->world; r++)
+        for (int j = 0; j < 4; j++)
+            if (c->opened[r][j]) cudaIpcCloseMemHandle(c->opened[r][j]);
+    if (c->comm) g_nccl.CommDestroy(c->comm);
+    if (c->d_small) cudaFree(c->d_small);
+    if (c->h_small) cudaFreeHost(c->h_small);
+    delete c;
+}
+
+int comm_allgather_f32(SlamComm *c, float *buf, size_t count, cudaStream_t st) {
+    NC(g_nccl.AllGather(buf + (size_t) c->rank * count, buf, count, ncclFloat32, c->comm, st));
+    return SLAMGPU_OK;
+}
+
+int comm_halo_unif(SlamComm *c, double *unif_base, size_t P, cudaStream_t st) {
+    NC(g_nccl.GroupStart());
+    if (c->rank + 1 < c->world) NC(g_nccl.Send(unif_base + P, 2, ncclFloat64, c->rank + 1, c->comm, st));
+    if (c->rank > 0) NC(g_nccl.Recv(unif_base, 2, ncclFloat64, c->rank - 1, c->comm, st));
+    NC(g_nccl.GroupEnd());
+    return SLAMGPU_OK;
+}
+
+static int barrier(SlamComm *c, cudaStream_t st) {
+    // stream-ordered: completes on a rank only once every rank's stream has reached it
+    float *b = (float *) (c->d_small + 2048);
+    NC(g_nccl.AllGather(b + c->rank, b, 1, ncclFloat32, c->comm, st));
+    return SLAMGPU_OK;
+}
+
+static int open_peers(SlamComm *c, slamgpu *h) {
+    if (c->peers_open) return SLAMGPU_OK;
+    cudaIpcMemHandle_t mine[4];
+    void *ptrs[4] = {h->pose[0], h->pose[1], h->lm_mean, h->lm_cov};
+    for (int j = 0; j < 4; j++) CU(cudaIpcGetMemHandle(&mine[j], ptrs[j]));
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is 64 bytes");
+    const size_t per = sizeof(mine);  // 256 B per rank
+    CU(cudaMemcpyAsync(c->d_small + (size_t) c->rank * per, mine, per, cudaMemcpyHostToDevice, h->stream));
+    NC(g_nccl.AllGather(c->d_small + (size_t) c->rank * per, c->d_small, per, ncclChar, c->comm, h->stream));
+    CU(cudaMemcpyAsync(c->h_small, c->d_small, per * c->world, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    for (int r = 0; r < c->world; r++) {
+        void *p[4];
+        if (r == c->rank) {
+            for (int j = 0; j < 4; j++) p[j] = ptrs[j];
+        } else {
+            cudaIpcMemHandle_t hd[4];
+            memcpy(hd, c->h_small + (size_t) r * per, per);
+            for (int j = 0; j < 4; j++) {
+                CU(cudaIpcOpenMemHandle(&p[j], hd[j], cudaIpcMemLazyEnablePeerAccess));
+                c->opened[r][j] = p[j];
+            }
+        }
+        c->peers.pose[0][r] = (const float *) p[0];
+        c->peers.pose[1][r] = (const float *) p[1];
+        c->peers.mean[r] = (const float2 *) p[2];
+        c->peers.cov[r] = (const float4 *) p[3];
+    }
+    c->peers_open = true;
+    return SLAMGPU_OK;
+}
+
+// ---- gather kernels with sources on any rank -------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_gather_pose_sharded(PeerMaps pm, int cur, float *__restrict__ dst_pose,
+                                                             float *__restrict__ w, const int *__restrict__ keep,
+                                                             size_t P, long long n_global, float new_w) {
+    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    long long k = keep[p];
+    if (k < 0) k = n_global - 1;
+    const int r = (int) (k / (long long) P);
+    const size_t sidx = (size_t) (k - (long long) r * (long long) P);
+    const float *src = pm.pose[cur][r];
+#pragma unroll
+    for (int c = 0; c < 12; c++) dst_pose[c * P + p] = src[c * P + sidx];
+    w[p] = new_w;
+}
+
+__global__ void __launch_bounds__(256) k_gather_rows_sharded(PeerMaps pm, MapRing m, size_t P,
+                                                             const int *__restrict__ keep, int l0, int nrows, int shift,
+                                                             long long n_global) {
+    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    long long k = keep[p];
+    if (k < 0) k = n_global - 1;
+    const int r = (int) (k / (long long) P);
+    const size_t sidx = (size_t) (k - (long long) r * (long long) P);
+    const float2 *smean = pm.mean[r];
+    const float4 *scov = pm.cov[r];
+    const int lbeg = l0 + blockIdx.y * SLAM_GATHER_ROWS;
+    float2 a[SLAM_GATHER_ROWS];
+    float4 c[SLAM_GATHER_ROWS];
+#pragma unroll
+    for (int q = 0; q < SLAM_GATHER_ROWS; q++) {
+        const int l = lbeg + q;
+        if (l < l0 + nrows) {
+            const int srow = (m.ring_base + l) % m.ring_rows;  // every rank's ring moves in lockstep
+            a[q] = smean[(size_t) srow * P + sidx];
+            c[q] = scov[(size_t) srow * P + sidx];
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < SLAM_GATHER_ROWS; q++) {
+        const int l = lbeg + q;
+        if (l < l0 + nrows) {
+            const int drow = (m.ring_base + l - shift + m.ring_rows) % m.ring_rows;
+            __stcs(&m.mean[(size_t) drow * P + p], a[q]);
+            __stcs(&m.cov[(size_t) drow * P + p], c[q]);
+        }
+    }
+}
+
+int comm_gather_sharded(SlamComm *c, slamgpu *h) {
+    RET(open_peers(c, h));
+    const size_t P = h->P;
+    const float new_w = 1.0f / (float) h->Pg;
+    const unsigned gx = (unsigned) ((P + 255) / 256);
+    // everyone's update kernels must have finished before any rank reads a peer's state
+    RET(barrier(c, h->stream));
+    k_gather_pose_sharded<<<gx, 256, 0, h->stream>>>(c->peers, h->cur, h->pose[h->cur ^ 1], h->w, h->keep, P,
+                                                     (long long) h->Pg, new_w);
+    CU(cudaGetLastError());
+    h->launches++;
+    h->t_launches[SLAMGPU_T_GATHER]++;
+    const int S = h->spare;
+    for (int l0 = 0; l0 < h->Nf; l0 += S) {
+        const int nrows = (h->Nf - l0 < S) ? h->Nf - l0 : S;
+        dim3 grid(gx, (nrows + SLAM_GATHER_ROWS - 1) / SLAM_GATHER_ROWS);
+        k_gather_rows_sharded<<<grid, 256, 0, h->stream>>>(c->peers, h->ring(), P, h->keep, l0, nrows, S,
+                                                           (long long) h->Pg);
+        CU(cudaGetLastError());
+        h->launches++;
+        h->t_launches[SLAMGPU_T_GATHER]++;
+        RET(barrier(c, h->stream));  // nobody may recycle these source rows before every rank has read them
+    }
+    if (h->Nf == 0) RET(barrier(c, h->stream));
+    h->cur ^= 1;
+    h->ring_base = (h->ring_base - S + h->ring_rows) % h->ring_rows;
+    return SLAMGPU_OK;
+}
+
+struct EstWire {
+    double sx, sy, theta;
+    long long imax;
+    float wmax;
+    float pad;
+};
+
+int comm_reduce_estimate(SlamComm *c, slamgpu *h, double *sx, double *sy, float wmax, long long imax, double *theta) {
+    EstWire mine;
+    mine.sx = *sx; mine.sy = *sy; mine.theta = *theta; mine.imax = imax; mine.wmax = wmax; mine.pad = 0;
+    EstWire *d = (EstWire *) c->d_small;
+    CU(cudaMemcpyAsync(d + c->rank, &mine, sizeof(mine), cudaMemcpyHostToDevice, h->stream));
+    NC(g_nccl.AllGather(d + c->rank, d, sizeof(EstWire), ncclChar, c->comm, h->stream));
+    CU(cudaMemcpyAsync(c->h_small, d, sizeof(EstWire) * c->world, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    const EstWire *all = (const EstWire *) c->h_small;
+    double tx = 0, ty = 0, th = 0;
+    float best = -INFINITY;
+    long long bi = 0x7fffffffffffffffLL;
+    for (int r = 0; r < c->world; r++) {  // rank order: identical result on every rank
+        tx += all[r].sx;
+        ty += all[r].sy;
+        if (all[r].wmax > best || (all[r].wmax == best && all[r].imax < bi)) {
+            best = all[r].wmax;
+            bi = all[r].imax;
+            th = all[r].theta;
+        }
+    }
+    *sx = tx; *sy = ty; *theta = th;
+    return SLAMGPU_OK;
+}

@@ -1,0 +1,117 @@
+// handle.h — private: the device-side state behind a slamgpu_t and the error helpers shared by capi.cu / comm.cu.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/slamgpu.h"
+#include "types.cuh"
+
+int slam_fail(int code, const std::string &msg);  // records the text for slamgpu_last_error(), returns code
+
+#define CU(call)                                                                                          \
+    do {                                                                                                  \
+        cudaError_t e_ = (call);                                                                          \
+        if (e_ != cudaSuccess)                                                                            \
+            return slam_fail(e_ == cudaErrorMemoryAllocation ? SLAMGPU_ENOMEM : SLAMGPU_ECUDA,            \
+                             std::string(#call) + ": " + cudaGetErrorString(e_) + " (" __FILE__ ":" +     \
+                                 std::to_string(__LINE__) + ")");                                         \
+    } while (0)
+#define RET(call)                        \
+    do {                                 \
+        int r_ = (call);                 \
+        if (r_ != SLAMGPU_OK) return r_; \
+    } while (0)
+
+struct SlamComm;
+using slam::EstPartial;
+using slam::MapRing;
+using slam::PoseSoA;
+
+struct Scalars {  // device + pinned mirror
+    float ws, s2, csum, neff;
+    int anomaly;
+    int pad[3];
+};
+
+struct TimedSpan {
+    cudaEvent_t a, b;
+    int which;
+};
+
+struct slamgpu {
+    slamgpu_config cfg;
+    size_t P = 0;         // local particles
+    size_t Pg = 0;        // global particles (== P unless sharded)
+    size_t slot0 = 0;     // first global particle held here
+    int rank = 0, world = 1;
+    int nf_cap = 0, Nf = 0, spare = 0, ring_rows = 0, ring_base = 0;
+    cudaStream_t stream = nullptr, own_stream = nullptr;
+    float *pose[2] = {nullptr, nullptr};  // each: xv[3][P] then Pv[9][P]
+    int cur = 0;
+    float *w = nullptr;
+    float2 *lm_mean = nullptr;
+    float4 *lm_cov = nullptr;
+    float *gauss = nullptr;      // [3][P] staged normals
+    double *unif_base = nullptr; // [2 + P] (2-slot halo in front for the sharded search)
+    float *di_base = nullptr;    // [2 + P]
+    float *cdf = nullptr, *mloc = nullptr;  // [Pg]
+    float *sel = nullptr;        // [P]
+    int *keep = nullptr;         // [P]
+    float *tot_w = nullptr, *tot_c = nullptr, *tot_s = nullptr, *bmax = nullptr;  // [nb_global]
+    size_t nb = 0, nbg = 0;      // local / global 1024-blocks
+    Scalars *d_sc = nullptr, *h_sc = nullptr;
+    float2 *d_z = nullptr;
+    int *d_row = nullptr;
+    float *d_rec_in = nullptr, *d_rec_out = nullptr;
+    size_t rec_cap = 0;
+    int obs_cap = 0;
+    void *h_obs = nullptr;       // pinned staging for the observation set
+    EstPartial *d_est = nullptr, *h_est = nullptr;
+    int est_blocks = 0;
+    bool gauss_staged = false, unif_staged = false;
+    int gauss_rows_staged = 0;
+    // timing
+    bool timing = false;
+    std::vector<TimedSpan> spans;
+    std::vector<cudaEvent_t> free_events;
+    double t_ms[SLAMGPU_T_COUNT] = {0};
+    int64_t t_events[SLAMGPU_T_COUNT] = {0};
+    int64_t t_launches[SLAMGPU_T_COUNT] = {0};
+    int64_t launches = 0;
+    SlamComm *comm = nullptr;
+
+    PoseSoA soa(int which) const {
+        PoseSoA s;
+        s.xv = pose[which];
+        s.Pv = pose[which] + 3 * P;
+        s.w = w;
+        return s;
+    }
+    MapRing ring() const {
+        MapRing m;
+        m.mean = lm_mean;
+        m.cov = lm_cov;
+        m.ring_rows = ring_rows;
+        m.ring_base = ring_base;
+        return m;
+    }
+    int phys_row(int l) const { return (ring_base + l) % ring_rows; }
+    double *unif() const { return unif_base + 2; }
+    float *di() const { return di_base + 2; }
+};
+
+
+// ---- comm.cu: NCCL / peer-memory exchange for the sharded resample -----------------------------------------
+int comm_unique_id(void *id128, std::string *err);
+SlamComm *comm_create(int rank, int world, const void *id128, int device, std::string *err);
+void comm_destroy(SlamComm *c);
+// In-place all-gather over a global array: this rank's count elements sit at buf + rank*count.
+int comm_allgather_f32(SlamComm *c, float *buf, size_t count, cudaStream_t st);
+// unif_base[0..1] <- the previous rank's last two uniforms (the search kernel's 2-slot halo).
+int comm_halo_unif(SlamComm *c, double *unif_base, size_t P, cudaStream_t st);
+// particles[i] = old[keep[i]] with sources on any rank (peer-mapped reads inside the gather kernels).
+int comm_gather_sharded(SlamComm *c, slamgpu *h);
+int comm_reduce_estimate(SlamComm *c, slamgpu *h, double *sx, double *sy, float wmax, long long imax, double *theta);

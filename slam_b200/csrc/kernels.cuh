@@ -1,0 +1,714 @@
+// kernels.cuh — the sm_100a kernels of the FastSLAM hot path.
+//
+// One thread owns one particle; state is structure-of-arrays so that every warp access is one contiguous
+// segment (pose planes: 128 B; landmark rows: float2 -> 256 B, float4 -> 512 B per warp).  Landmark rows live in a
+// ring of (nf_cap + spare) physical rows: logical row l is physical row (ring_base + l) % ring_rows, which lets the
+// resample gather move the whole map without a second full-size buffer (gather_rows below).
+//
+// All contractions are 2x2 / 3x3 per particle: CUDA-core fp32, no tensor cores (nothing here is GEMM shaped).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "slam_math.cuh"
+#include "types.cuh"
+
+namespace slam {
+
+struct PredictArgs {
+    float V, G, Q[4], dt, phi_true, wheel_base, sigma_phi;
+    int method, use_heading;
+};
+
+__device__ __forceinline__ void load_pose(const PoseSoA &s, size_t P, size_t p, float *x, float *C) {
+#pragma unroll
+    for (int c = 0; c < 3; c++) x[c] = s.xv[c * P + p];
+    if (C) {
+#pragma unroll
+        for (int j = 0; j < 9; j++) C[j] = s.Pv[j * P + p];
+    }
+}
+__device__ __forceinline__ void store_pose(const PoseSoA &s, size_t P, size_t p, const float *x, const float *C) {
+#pragma unroll
+    for (int c = 0; c < 3; c++) s.xv[c * P + p] = x[c];
+    if (C) {
+#pragma unroll
+        for (int j = 0; j < 9; j++) s.Pv[j * P + p] = C[j];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K1  predict: FastSLAM{1,2}::predict over all particles (fastslam2.cpp:51-60, fastslam1.cpp:57-66).
+// gauss: nullptr or [2][P] standard normals.  96 B of state traffic per particle (FastSLAM2).
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_predict(PoseSoA s, size_t P, PredictArgs a, const float *__restrict__ gauss) {
+    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    const bool need_cov = (a.method == 2) || a.use_heading;
+    float x[3], C[9];
+    load_pose(s, P, p, x, need_cov ? C : nullptr);
+    float g2[2];
+    if (gauss) {
+        g2[0] = gauss[p];
+        g2[1] = gauss[P + p];
+    }
+    predict_particle(a.method, x, C, a.V, a.G, a.Q, a.dt, a.phi_true, a.wheel_base, a.sigma_phi, a.use_heading != 0,
+                     gauss ? g2 : nullptr);
+    store_pose(s, P, p, x, need_cov ? C : nullptr);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K3  FastSLAM2 per-particle update: sampleProposal (fastslam2.cpp:290-368) -> likelihoodGivenXv (370-400) ->
+// featureUpdate (core.cpp:132-175), fused.  The observation set (z, physical landmark row) is staged in shared
+// memory once per CTA.  Pass 1 walks the K observed landmarks sequentially refining the pose proposal (read only);
+// pass 2 re-reads them at the sampled pose, multiplies the likelihood and writes the updated landmark back.
+// Algorithmic traffic: 48 B per particle-landmark + 116 B per particle.
+// ---------------------------------------------------------------------------------------------------------
+struct ObsSet {           // device arrays written by the host before the launch
+    const float2 *z;      // [K] range, bearing
+    const int *row;       // [K] PHYSICAL landmark row
+};
+
+__device__ __forceinline__ void lm_load(const MapRing &m, size_t P, int row, size_t p, float *xf, float *Pf) {
+    const float2 a = m.mean[(size_t) row * P + p];
+    const float4 c = m.cov[(size_t) row * P + p];
+    xf[0] = a.x; xf[1] = a.y;
+    Pf[0] = c.x; Pf[1] = c.z; Pf[2] = c.y; Pf[3] = c.w;  // column-major linear -> row-major
+}
+__device__ __forceinline__ void lm_store(const MapRing &m, size_t P, int row, size_t p, const float *xf,
+                                         const float *Pf) {
+    __stcs(&m.mean[(size_t) row * P + p], make_float2(xf[0], xf[1]));
+    __stcs(&m.cov[(size_t) row * P + p], make_float4(Pf[0], Pf[2], Pf[1], Pf[3]));
+}
+
+extern __shared__ __align__(16) unsigned char slam_smem[];
+
+__device__ __forceinline__ void stage_obs(const ObsSet &o, int K, float2 *&sz, int *&srow) {
+    sz = reinterpret_cast<float2 *>(slam_smem);
+    srow = reinterpret_cast<int *>(sz + K);
+    for (int i = threadIdx.x; i < K; i += blockDim.x) {
+        sz[i] = o.z[i];
+        srow[i] = o.row[i];
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(128) k_fs2_update(PoseSoA s, MapRing m, size_t P, ObsSet o, int K, float4 Rm,
+                                                    const float *__restrict__ gauss) {
+    float2 *sz;
+    int *srow;
+    stage_obs(o, K, sz, srow);
+    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    const float R[4] = {Rm.x, Rm.y, Rm.z, Rm.w};
+    float x[3], C[9], x0[3], C0[9];
+    load_pose(s, P, p, x, C);
+#pragma unroll
+    for (int j = 0; j < 3; j++) x0[j] = x[j];
+#pragma unroll
+    for (int j = 0; j < 9; j++) C0[j] = C[j];
+    const float g3[3] = {gauss[p], gauss[P + p], gauss[2 * P + p]};
+    float wgt = s.w[p];
+
+    // pass 1: proposal, sequential over observations, next landmark prefetched while this one is processed
+    float xf[2], Pf[4], nxf[2], nPf[4];
+    lm_load(m, P, srow[0], p, nxf, nPf);
+    for (int i = 0; i < K; i++) {
+        xf[0] = nxf[0]; xf[1] = nxf[1];
+#pragma unroll
+        for (int j = 0; j < 4; j++) Pf[j] = nPf[j];
+        if (i + 1 < K) lm_load(m, P, srow[i + 1], p, nxf, nPf);
+        const float z[2] = {sz[i].x, sz[i].y};
+        proposal_step(x, C, R, xf, Pf, z);
+    }
+    // sample the pose (fastslam2.cpp:352-357) and the two pose-space Gaussian arguments (359-362)
+    float xs[3];
+    multivariate_gauss<3>(x, C, g3, xs);
+    const float v1[3] = {x0[0] - xs[0], x0[1] - xs[1], trig_offset(x0[2] - xs[2])};
+    const float v2[3] = {x[0] - xs[0], x[1] - xs[1], trig_offset(x[2] - xs[2])};
+    const float prior = gauss_evaluate<3>(v1, C0);
+    const float prop = gauss_evaluate<3>(v2, C);
+
+    // pass 2: likelihood at the sampled pose + landmark EKF, independent per observation
+    float like = 1.0f;
+    lm_load(m, P, srow[0], p, nxf, nPf);
+    for (int i = 0; i < K; i++) {
+        xf[0] = nxf[0]; xf[1] = nxf[1];
+#pragma unroll
+        for (int j = 0; j < 4; j++) Pf[j] = nPf[j];
+        if (i + 1 < K) lm_load(m, P, srow[i + 1], p, nxf, nPf);
+        const float z[2] = {sz[i].x, sz[i].y};
+        like = like * likelihood_and_feature_update(xs, R, xf, Pf, z);
+        lm_store(m, P, srow[i], p, xf, Pf);
+    }
+    wgt = wgt * like * prior / prop;  // fastslam2.cpp:367
+    s.w[p] = wgt;
+    const float Z[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};  // Pv is zeroed after sampling, fastslam2.cpp:355-357
+    store_pose(s, P, p, xs, Z);
+}
+
+// K3'  FastSLAM1 per-particle update: computeWeight (fastslam1.cpp:91-118) + featureUpdate, one pass.
+__global__ void __launch_bounds__(256) k_fs1_update(PoseSoA s, MapRing m, size_t P, ObsSet o, int K, float4 Rm) {
+    float2 *sz;
+    int *srow;
+    stage_obs(o, K, sz, srow);
+    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    const float R[4] = {Rm.x, Rm.y, Rm.z, Rm.w};
+    float x[3];
+    load_pose(s, P, p, x, nullptr);
+    float wt = 1.0f;
+    float xf[2], Pf[4], nxf[2], nPf[4];
+    lm_load(m, P, srow[0], p, nxf, nPf);
+    for (int i = 0; i < K; i++) {
+        xf[0] = nxf[0]; xf[1] = nxf[1];
+#pragma unroll
+        for (int j = 0; j < 4; j++) Pf[j] = nPf[j];
+        if (i + 1 < K) lm_load(m, P, srow[i + 1], p, nxf, nPf);
+        const float z[2] = {sz[i].x, sz[i].y};
+        fs1_weight_and_feature_update(x, R, xf, Pf, z, &wt);
+        lm_store(m, P, srow[i], p, xf, Pf);
+    }
+    s.w[p] = s.w[p] * wt;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K4  addFeature (core.cpp:479-509) for Kn new observations at PHYSICAL rows o.row[i].  sample_first implements
+// FastSLAM2's "no known landmark this step" branch (fastslam2.cpp:36-42): xv ~ N(xv, Pv), Pv = 0 first.
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_add_feature(PoseSoA s, MapRing m, size_t P, ObsSet o, int Kn, float4 Rm,
+                                                     int sample_first, const float *__restrict__ gauss) {
+    float2 *sz;
+    int *srow;
+    stage_obs(o, Kn, sz, srow);
+    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    const float R[4] = {Rm.x, Rm.y, Rm.z, Rm.w};
+    float x[3];
+    if (sample_first) {
+        float C[9], xs[3];
+        load_pose(s, P, p, x, C);
+        const float g3[3] = {gauss[p], gauss[P + p], gauss[2 * P + p]};
+        multivariate_gauss<3>(x, C, g3, xs);
+        const float Z[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+        store_pose(s, P, p, xs, Z);
+        x[0] = xs[0]; x[1] = xs[1]; x[2] = xs[2];
+    } else {
+        load_pose(s, P, p, x, nullptr);
+    }
+    for (int i = 0; i < Kn; i++) {
+        float xf[2], Pf[4];
+        add_feature_one(x, sz[i].x, sz[i].y, R, xf, Pf);
+        lm_store(m, P, srow[i], p, xf, Pf);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K2  batched computeJacobians over the resident particle set: out[(i*P+p)*16 + 0..15] in the accelerator
+// record order zp[2], Hf[4], Hv[6], Sf[4] (core.cpp:624-664).  64 B written per particle-landmark.
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void jacobian_record(const float *x, const float *R, const float *xf, const float *Pf,
+                                                float4 *out) {
+    float zp[2], Hf[4], Hv[6], Sf[4];
+    jacobian_one(x, R, xf, Pf, zp, Hf, Sf);
+    hv_from_hf(Hf, Hv);
+    out[0] = make_float4(zp[0], zp[1], Hf[0], Hf[1]);
+    out[1] = make_float4(Hf[2], Hf[3], Hv[0], Hv[1]);
+    out[2] = make_float4(Hv[2], Hv[3], Hv[4], Hv[5]);
+    out[3] = make_float4(Sf[0], Sf[1], Sf[2], Sf[3]);
+}
+
+__global__ void __launch_bounds__(256) k_jacobians_batch(PoseSoA s, MapRing m, size_t P, ObsSet o, int K, float4 Rm,
+                                                         float4 *__restrict__ out) {
+    float2 *sz;
+    int *srow;
+    stage_obs(o, K, sz, srow);
+    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    const float R[4] = {Rm.x, Rm.y, Rm.z, Rm.w};
+    float x[3];
+    load_pose(s, P, p, x, nullptr);
+    for (int i = 0; i < K; i++) {
+        float xf[2], Pf[4];
+        lm_load(m, P, srow[i], p, xf, Pf);
+        jacobian_record(x, R, xf, Pf, out + ((size_t) i * P + p) * 4);
+    }
+}
+
+// The literal accelerator record for ONE particle (core.cpp:586-664): thread i handles landmark i.
+__global__ void k_jacobians_record(const float *__restrict__ in, int n, float4 *__restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float x[3] = {in[0], in[1], in[2]};
+    const float R[4] = {in[3], in[5], in[4], in[6]};
+    const float *r = in + 7 + 6 * i;
+    const float xf[2] = {r[0], r[1]};
+    const float Pf[4] = {r[2], r[4], r[3], r[5]};
+    jacobian_record(x, R, xf, Pf, out + (size_t) i * 4);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K5/K6  weights -> CDF -> keep[]  (resampleParticles core.cpp:718-734, stratifiedResample 780-807)
+//
+// BLOCKED order (SLAMGPU_SCAN_BLOCKED): the fixed-shape inclusive scan of oracle/slam_oracle.c blocked_scan():
+//   a block = SLAM_SCAN_BLOCK consecutive elements, one per thread; each warp scans its 32 elements with the
+//   Hillis-Steele ladder (x += shfl_up(x, d), d = 1..16), the 32 warp totals are scanned by the same ladder, and
+//   element = warp_exclusive + local.  Block totals are scanned recursively by the same shape.  Every add is one
+//   fp32 add, so the result does not depend on how many devices hold the blocks.
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float ladder32(float v, int lane) {
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const float t = __shfl_up_sync(0xffffffffu, v, d);
+        if (lane >= d) v = __fadd_rn(v, t);
+    }
+    return v;
+}
+__device__ __forceinline__ float ladder32_max(float v, int lane) {
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const float t = __shfl_up_sync(0xffffffffu, v, d);
+        if (lane >= d) v = fmaxf(v, t);
+    }
+    return v;
+}
+
+// Inclusive blocked scan of one 1024-element block held one element per thread.  sh: 32 floats of shared memory.
+__device__ __forceinline__ float block_scan_1024(float v, float *sh) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const float loc = ladder32(v, lane);
+    __syncthreads();  // sh may still be read by a previous call
+    if (lane == 31) sh[wid] = loc;
+    __syncthreads();
+    if (wid == 0) sh[lane] = ladder32(sh[lane], lane);
+    __syncthreads();
+    return (wid > 0) ? __fadd_rn(sh[wid - 1], loc) : loc;
+}
+__device__ __forceinline__ float block_maxscan_1024(float v, float *sh) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const float loc = ladder32_max(v, lane);
+    __syncthreads();
+    if (lane == 31) sh[wid] = loc;
+    __syncthreads();
+    if (wid == 0) sh[lane] = ladder32_max(sh[lane], lane);
+    __syncthreads();
+    return (wid > 0) ? fmaxf(sh[wid - 1], loc) : loc;
+}
+
+// Step A: per-block totals of w.  tot[b] = last live element of the block's local scan.
+__global__ void __launch_bounds__(SLAM_SCAN_BLOCK) k_block_totals(const float *__restrict__ w, size_t n,
+                                                                  float *__restrict__ tot) {
+    __shared__ float sh[32];
+    const size_t i = (size_t) blockIdx.x * SLAM_SCAN_BLOCK + threadIdx.x;
+    const float v = (i < n) ? w[i] : 0.0f;
+    const float sc = block_scan_1024(v, sh);
+    const size_t last = min(n, ((size_t) blockIdx.x + 1) * SLAM_SCAN_BLOCK) - 1;
+    if (i == last) tot[blockIdx.x] = sc;
+}
+
+// Steps B/D: the recursive part of the blocked scan over a totals array, by ONE CTA of 1024 threads, in place.
+// Handles n <= 1024*1024 totals (P <= 2^30): chunks of 1024 are scanned locally one after the other, the chunk
+// totals are scanned as one block (that is the recursion's last level), and added back.
+// blockIdx.x selects one of up to 3 independent arrays.  sum_out[blockIdx.x] = last element of the scan.
+struct UpperArgs {
+    float *arr[3];
+    float *sum_out[3];
+    int n;
+    int use_max;  // 1: max-scan (exact, order free) instead of the add scan
+};
+__global__ void __launch_bounds__(SLAM_SCAN_BLOCK) k_scan_upper(UpperArgs a) {
+    __shared__ float sh[32];
+    __shared__ float chunk_tot[SLAM_SCAN_BLOCK];
+    float *x = a.arr[blockIdx.x];
+    const int n = a.n;
+    const int nchunk = (n + SLAM_SCAN_BLOCK - 1) / SLAM_SCAN_BLOCK;
+    for (int c = 0; c < nchunk; c++) {
+        const int i = c * SLAM_SCAN_BLOCK + threadIdx.x;
+        const float v = (i < n) ? x[i] : (a.use_max ? -INFINITY : 0.0f);
+        const float sc = a.use_max ? block_maxscan_1024(v, sh) : block_scan_1024(v, sh);
+        if (i < n) x[i] = sc;
+        const int last = min(n, (c + 1) * SLAM_SCAN_BLOCK) - 1;
+        if (i == last) chunk_tot[c] = sc;
+    }
+    __syncthreads();
+    if (nchunk > 1) {
+        const float v = ((int) threadIdx.x < nchunk) ? chunk_tot[threadIdx.x] : (a.use_max ? -INFINITY : 0.0f);
+        const float sc = a.use_max ? block_maxscan_1024(v, sh) : block_scan_1024(v, sh);
+        __syncthreads();
+        if ((int) threadIdx.x < nchunk) chunk_tot[threadIdx.x] = sc;
+        __syncthreads();
+        for (int c = 1; c < nchunk; c++) {
+            const int i = c * SLAM_SCAN_BLOCK + threadIdx.x;
+            if (i < n) x[i] = a.use_max ? fmaxf(chunk_tot[c - 1], x[i]) : __fadd_rn(chunk_tot[c - 1], x[i]);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && a.sum_out[blockIdx.x]) *a.sum_out[blockIdx.x] = x[n - 1];
+}
+
+// Step C: normalise (core.cpp:727-729 / 784-786: one quotient serves both), local CDF scan, totals of w and w^2.
+// pow(w,2) is a double product stored as float == one correctly rounded fp32 multiply.
+__global__ void __launch_bounds__(SLAM_SCAN_BLOCK) k_normalise_scan(float *__restrict__ w, size_t n,
+                                                                    const float *__restrict__ ws_ptr,
+                                                                    float *__restrict__ cdf_local,
+                                                                    float *__restrict__ tot_c,
+                                                                    float *__restrict__ tot_s) {
+    __shared__ float sh[32];
+    const size_t i = (size_t) blockIdx.x * SLAM_SCAN_BLOCK + threadIdx.x;
+    const float ws = *ws_ptr;
+    float wn = 0.0f;
+    if (i < n) {
+        wn = __fdiv_rn(w[i], ws);
+        w[i] = wn;
+    }
+    const float sq = __fmul_rn(wn, wn);
+    const float sc = block_scan_1024(wn, sh);
+    const float ss = block_scan_1024(sq, sh);
+    if (i < n) cdf_local[i] = sc;
+    const size_t last = min(n, ((size_t) blockIdx.x + 1) * SLAM_SCAN_BLOCK) - 1;
+    if (i == last) {
+        tot_c[blockIdx.x] = sc;
+        tot_s[blockIdx.x] = ss;
+    }
+}
+
+// Step E: cdf = block_exclusive + local; in-block running maximum (mloc) and block maximum (bmax) so that the
+// search below runs on monotone keys even where the tree-ordered CDF dips by an ulp.
+// tot_c_scanned is indexed by GLOBAL block (block_offset = first global block of this device).
+__global__ void __launch_bounds__(SLAM_SCAN_BLOCK) k_cdf_finalise(float *__restrict__ cdf, size_t n,
+                                                                  const float *__restrict__ tot_c_scanned,
+                                                                  size_t block_offset, float *__restrict__ mloc,
+                                                                  float *__restrict__ bmax) {
+    __shared__ float sh[32];
+    const size_t i = (size_t) blockIdx.x * SLAM_SCAN_BLOCK + threadIdx.x;
+    const size_t gb = block_offset + blockIdx.x;
+    float v = -INFINITY;
+    if (i < n) {
+        v = cdf[i];
+        if (gb > 0) v = __fadd_rn(tot_c_scanned[gb - 1], v);
+        cdf[i] = v;
+    }
+    const float mx = block_maxscan_1024(v, sh);
+    if (i < n) mloc[i] = mx;
+    const size_t last = min(n, ((size_t) blockIdx.x + 1) * SLAM_SCAN_BLOCK) - 1;
+    if (i == last) bmax[blockIdx.x] = mx;
+}
+
+// Step F: select[] (stratifiedRandom core.cpp:751-769; di precomputed by the reference's own fp32 accumulation
+// on the host) and keep[] (the merge at core.cpp:800-806) as a search.
+//
+// G(c) = first global index i with cdf[i] > select[c] (two-level: block maxima prefix BM, then the in-block running
+// maximum).  The sequential merge gives keep[c] = first i >= keep[c-1] with cdf[i] > select[c]; with
+// K[c] = max(G[c], G[c-1]) this equals K[c] whenever, for every c, either G[c] >= K[c-1], or K[c] == K[c-1] and
+// cdf[K[c-1]] > select[c] (induction on c).  The kernel checks exactly that and raises *anomaly otherwise, in
+// which case the host runs the exact sequential merge (k_keep_sequential).  keep = -1 where the reference leaves -1.
+struct SearchArgs {
+    const float *di;       // [n_local] strata midpoints for this device's global slots
+    const double *unif;    // [n_local]
+    const float *cdf;      // [n_global] (all-gathered when sharded)
+    const float *mloc;     // [n_global]
+    const float *BM;       // [nb_global] prefix maxima of the block maxima
+    float *sel;            // [n_local] out
+    int *keep;             // [n_local] out (global indices)
+    int *anomaly;          // out flag
+    size_t n_local, n_global, slot_offset;
+    int nb_global;
+    float k, khalf;        // 1/N and k/2 as the reference forms them
+};
+
+__device__ __forceinline__ float select_value(const SearchArgs &a, size_t c_local) {
+    // *diter + unifRand()*k - k/2 evaluated in double, stored as float (core.cpp:767)
+    const double t = __dadd_rn((double) a.di[c_local], __dmul_rn(a.unif[c_local], (double) a.k));
+    return __double2float_rn(__dsub_rn(t, (double) a.khalf));
+}
+
+__device__ __forceinline__ long long first_exceed(const SearchArgs &a, float s) {
+    // first block whose prefix-max exceeds s
+    int lo = 0, hi = a.nb_global;  // answer in [lo, hi]; hi == nb_global means none
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (a.BM[mid] > s) hi = mid; else lo = mid + 1;
+    }
+    if (lo == a.nb_global) return (long long) a.n_global;  // sentinel: never assigned
+    const size_t b0 = (size_t) lo * SLAM_SCAN_BLOCK;
+    const int len = (int) min((size_t) SLAM_SCAN_BLOCK, a.n_global - b0);
+    int l = 0, h = len - 1;  // the block's last running max exceeds s, so an answer exists
+    while (l < h) {
+        const int mid = (l + h) >> 1;
+        if (a.mloc[b0 + mid] > s) h = mid; else l = mid + 1;
+    }
+    return (long long) (b0 + l);
+}
+
+__global__ void __launch_bounds__(256) k_search_keep(SearchArgs a) {
+    __shared__ long long g_sh[256 + 2];
+    const size_t c = (size_t) blockIdx.x * blockDim.x + threadIdx.x;  // local slot
+    const size_t c0 = (size_t) blockIdx.x * blockDim.x;
+    float s = 0.0f;
+    long long g = -1;
+    if (c < a.n_local) {
+        s = select_value(a, c);
+        a.sel[c] = s;
+        g = first_exceed(a, s);
+    }
+    g_sh[threadIdx.x + 2] = g;
+    if (threadIdx.x < 2) {
+        // halo: G of the two slots before this CTA's first one (global slots; none before global slot 0).
+        // Slots of the previous device are recomputed from its di/unif only when they are local; across a device
+        // boundary the host passes di/unif with a 2-slot halo (see capi), so index c0 - 2 + t is valid when
+        // slot_offset + c0 >= 2 - t.
+        const long long gc = (long long) (a.slot_offset + c0) - 2 + threadIdx.x;
+        long long gh = -1;
+        if (gc >= 0) {
+            SearchArgs h = a;
+            const long long cl = (long long) c0 - 2 + threadIdx.x;  // may be -1 / -2: halo stored before index 0
+            const double t = __dadd_rn((double) a.di[cl], __dmul_rn(a.unif[cl], (double) a.k));
+            const float sh_ = __double2float_rn(__dsub_rn(t, (double) a.khalf));
+            gh = first_exceed(h, sh_);
+        }
+        g_sh[threadIdx.x] = gh;
+    }
+    __syncthreads();
+    if (c >= a.n_local) return;
+    const long long g1 = g_sh[threadIdx.x + 1], g2 = g_sh[threadIdx.x];  // G[c-1], G[c-2]  (-1 if absent)
+    const long long kc = max(g, g1);
+    const long long kprev = max(g1, g2);  // K[c-1]; -1 when c is global slot 0
+    const long long SENT = (long long) a.n_global;
+    bool ok;
+    if (g >= kprev) ok = true;
+    else ok = (kc == kprev) && (kprev == SENT || a.cdf[kprev] > s);
+    if (!ok) atomicExch(a.anomaly, 1);
+    a.keep[c] = (kc == SENT) ? -1 : (int) kc;
+}
+
+// The exact sequential merge of core.cpp:800-806 (fallback when k_search_keep reports an anomaly, and the tail of
+// REFERENCE mode).  One thread; sel/cdf/keep global.
+__global__ void k_keep_sequential(const float *__restrict__ sel, const float *__restrict__ cdf, int *__restrict__ keep,
+                                  size_t n) {
+    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    for (size_t i = 0; i < n; i++) keep[i] = -1;
+    size_t ctr = 0;
+    for (size_t i = 0; i < n; i++) {
+        const float ci = cdf[i];
+        while (ctr < n && sel[ctr] < ci) {
+            keep[ctr] = (int) i;
+            ctr++;
+        }
+    }
+}
+
+// REFERENCE order (SLAMGPU_SCAN_REFERENCE): one thread reproduces Eigen's SSE redux (Redux.h:193-248 with the SSE2
+// predux of PacketMath.h:406-410) for both sums and the sequential fp32 running sum of cumulativeSum
+// (core.cpp:813-824).  Meant for the reference's own particle counts (100 .. ~10^4).
+__device__ float eigen_sum_seq(const float *v, long n) {
+    const long ps = 4;
+    const long size2 = (n / (2 * ps)) * (2 * ps);
+    const long size1 = (n / ps) * ps;
+    float res;
+    if (size1) {
+        float p0[4], p1[4];
+        for (int j = 0; j < 4; j++) p0[j] = v[j];
+        if (size1 > ps) {
+            for (int j = 0; j < 4; j++) p1[j] = v[ps + j];
+            for (long idx = 2 * ps; idx < size2; idx += 2 * ps)
+                for (int j = 0; j < 4; j++) {
+                    p0[j] = __fadd_rn(p0[j], v[idx + j]);
+                    p1[j] = __fadd_rn(p1[j], v[idx + ps + j]);
+                }
+            for (int j = 0; j < 4; j++) p0[j] = __fadd_rn(p0[j], p1[j]);
+            if (size1 > size2)
+                for (int j = 0; j < 4; j++) p0[j] = __fadd_rn(p0[j], v[size2 + j]);
+        }
+        res = __fadd_rn(__fadd_rn(p0[0], p0[2]), __fadd_rn(p0[1], p0[3]));
+        for (long idx = size1; idx < n; idx++) res = __fadd_rn(res, v[idx]);
+    } else {
+        res = v[0];
+        for (long idx = 1; idx < n; idx++) res = __fadd_rn(res, v[idx]);
+    }
+    return res;
+}
+
+__global__ void k_reference_weights(float *__restrict__ w, size_t n, const float *__restrict__ di,
+                                    const double *__restrict__ unif, float k, float khalf, float *__restrict__ sq,
+                                    float *__restrict__ cdf, float *__restrict__ sel, float *__restrict__ neff_out) {
+    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    const float ws = eigen_sum_seq(w, (long) n);
+    for (size_t i = 0; i < n; i++) {
+        const float wn = __fdiv_rn(w[i], ws);
+        w[i] = wn;
+        sq[i] = __fmul_rn(wn, wn);
+    }
+    const float s2 = eigen_sum_seq(sq, (long) n);
+    *neff_out = __fdiv_rn(1.0f, s2);
+    float run = 0.0f;
+    for (size_t i = 0; i < n; i++) {
+        run = __fadd_rn(run, w[i]);
+        cdf[i] = run;
+        const double t = __dadd_rn((double) di[i], __dmul_rn(unif[i], (double) k));
+        sel[i] = __double2float_rn(__dsub_rn(t, (double) khalf));
+    }
+}
+
+__global__ void k_neff(const float *__restrict__ s2, float *__restrict__ neff_out) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) *neff_out = __fdiv_rn(1.0f, *s2);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K7  resample gather: particles[i] = old[keep[i]], w = 1/N (core.cpp:736-748).  keep < 0 (undefined behaviour in
+// the reference) clamps to the last particle.  Local variant: every source index lies on this device
+// (src_offset = first global index held here).
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_gather_pose(const float *__restrict__ src_xv, const float *__restrict__ src_Pv,
+                                                     float *__restrict__ dst_xv, float *__restrict__ dst_Pv,
+                                                     float *__restrict__ w, const int *__restrict__ keep, size_t P,
+                                                     long long src_offset, long long n_global, float new_w) {
+    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    long long k = keep[p];
+    if (k < 0) k = n_global - 1;
+    const size_t sidx = (size_t) (k - src_offset);
+#pragma unroll
+    for (int c = 0; c < 3; c++) dst_xv[c * P + p] = src_xv[c * P + sidx];
+#pragma unroll
+    for (int c = 0; c < 9; c++) dst_Pv[c * P + p] = src_Pv[c * P + sidx];
+    w[p] = new_w;
+}
+
+// Rows [l0, l0 + nrows) of the map, logical -> shifted ring position.  grid = (ceil(P/256), row groups); each thread
+// keeps its source index in a register and moves ROWS_PER_THREAD rows (independent loads in flight).  keep is
+// non-decreasing, so reads are monotone with duplicates served by L1/L2, writes are fully coalesced.
+__global__ void __launch_bounds__(256) k_gather_rows(MapRing m, size_t P, const int *__restrict__ keep, int l0,
+                                                     int nrows, int shift, long long src_offset, long long n_global) {
+    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    long long k = keep[p];
+    if (k < 0) k = n_global - 1;
+    const size_t sidx = (size_t) (k - src_offset);
+    const int lbeg = l0 + blockIdx.y * SLAM_GATHER_ROWS;
+    float2 a[SLAM_GATHER_ROWS];
+    float4 c[SLAM_GATHER_ROWS];
+#pragma unroll
+    for (int r = 0; r < SLAM_GATHER_ROWS; r++) {
+        const int l = lbeg + r;
+        if (l < l0 + nrows) {
+            const int srow = (m.ring_base + l) % m.ring_rows;
+            a[r] = m.mean[(size_t) srow * P + sidx];
+            c[r] = m.cov[(size_t) srow * P + sidx];
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < SLAM_GATHER_ROWS; r++) {
+        const int l = lbeg + r;
+        if (l < l0 + nrows) {
+            const int drow = (m.ring_base + l - shift + m.ring_rows) % m.ring_rows;
+            __stcs(&m.mean[(size_t) drow * P + p], a[r]);
+            __stcs(&m.cov[(size_t) drow * P + p], c[r]);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K8  pose estimate (ParticleSLAMWrapper.cpp:56-77): double sums of x and y, heading of the FIRST max-weight
+// particle.  Two stages, fixed shape.
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void est_combine(EstPartial &a, const EstPartial &b) {
+    a.sx += b.sx;
+    a.sy += b.sy;
+    if (b.wmax > a.wmax || (b.wmax == a.wmax && b.imax < a.imax)) {
+        a.wmax = b.wmax;
+        a.imax = b.imax;
+    }
+}
+__device__ __forceinline__ EstPartial est_block_reduce(EstPartial v) {
+    __shared__ EstPartial sh[32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        EstPartial o;
+        o.sx = __shfl_down_sync(0xffffffffu, v.sx, d);
+        o.sy = __shfl_down_sync(0xffffffffu, v.sy, d);
+        o.wmax = __shfl_down_sync(0xffffffffu, v.wmax, d);
+        o.imax = __shfl_down_sync(0xffffffffu, v.imax, d);
+        est_combine(v, o);
+    }
+    if (lane == 0) sh[wid] = v;
+    __syncthreads();
+    const int nw = blockDim.x >> 5;
+    if (wid == 0) {
+        EstPartial z;
+        z.sx = 0; z.sy = 0; z.wmax = -INFINITY; z.imax = 0x7fffffffffffffffLL;
+        v = (lane < nw) ? sh[lane] : z;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            EstPartial o;
+            o.sx = __shfl_down_sync(0xffffffffu, v.sx, d);
+            o.sy = __shfl_down_sync(0xffffffffu, v.sy, d);
+            o.wmax = __shfl_down_sync(0xffffffffu, v.wmax, d);
+            o.imax = __shfl_down_sync(0xffffffffu, v.imax, d);
+            est_combine(v, o);
+        }
+    }
+    return v;
+}
+__global__ void __launch_bounds__(256) k_estimate_partial(const float *__restrict__ xv, const float *__restrict__ w,
+                                                          size_t P, long long offset, EstPartial *__restrict__ part) {
+    EstPartial v;
+    v.sx = 0; v.sy = 0; v.wmax = -INFINITY; v.imax = 0x7fffffffffffffffLL;
+    for (size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x; p < P; p += (size_t) gridDim.x * blockDim.x) {
+        EstPartial o;
+        o.sx = xv[p];
+        o.sy = xv[P + p];
+        o.wmax = w[p];
+        o.imax = offset + (long long) p;
+        est_combine(v, o);
+    }
+    v = est_block_reduce(v);
+    if (threadIdx.x == 0) part[blockIdx.x] = v;
+}
+__global__ void __launch_bounds__(256) k_estimate_final(const EstPartial *__restrict__ part, int n,
+                                                        const float *__restrict__ xv, size_t P, long long offset,
+                                                        EstPartial *__restrict__ out) {
+    EstPartial v;
+    v.sx = 0; v.sy = 0; v.wmax = -INFINITY; v.imax = 0x7fffffffffffffffLL;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) est_combine(v, part[i]);
+    v = est_block_reduce(v);
+    if (threadIdx.x == 0) {
+        const long long loc = v.imax - offset;
+        v.theta = (loc >= 0 && loc < (long long) P) ? xv[2 * P + (size_t) loc] : 0.0f;
+        *out = v;
+    }
+}
+
+// Strided download helper: every stride-th particle's pose and landmark means, packed.
+__global__ void __launch_bounds__(256) k_decimate(PoseSoA s, MapRing m, size_t P, size_t stride, size_t n, int Nf,
+                                                  float *__restrict__ xv_out, float2 *__restrict__ lm_out) {
+    const size_t q = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n) return;
+    const size_t p = q * stride;
+    for (int c = 0; c < 3; c++) xv_out[c * n + q] = s.xv[c * P + p];
+    if (lm_out)
+        for (int l = 0; l < Nf; l++) {
+            const int row = (m.ring_base + l) % m.ring_rows;
+            lm_out[(size_t) l * n + q] = m.mean[(size_t) row * P + p];
+        }
+}
+
+// Synthetic-workload initialisation: replicate a tile of Pt particles over all P (dst[p] = tile[p % Pt]).
+__global__ void __launch_bounds__(256) k_tile_planes(const float *__restrict__ tile, size_t Pt, float *__restrict__ dst,
+                                                     size_t P, int planes) {
+    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    for (int c = 0; c < planes; c++) dst[c * P + p] = tile[c * Pt + p % Pt];
+}
+__global__ void __launch_bounds__(256) k_tile_rows(const float2 *__restrict__ tmean, const float4 *__restrict__ tcov,
+                                                   size_t Pt, MapRing m, size_t P, int l0) {
+    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    const int l = blockIdx.y;  // row inside the uploaded chunk
+    const int row = (m.ring_base + l0 + l) % m.ring_rows;
+    m.mean[(size_t) row * P + p] = tmean[(size_t) l * Pt + p % Pt];
+    m.cov[(size_t) row * P + p] = tcov[(size_t) l * Pt + p % Pt];
+}
+
+}  // namespace slam

@@ -90,39 +90,4 @@ class Drive:
         return self.rng.integers(1, RAND_MAX, size=n).astype(np.int32)
 
 
-def synthetic_state(P, Nf, K, seed=1, extent=100.0, nf_cap=None):
-    """cfg-4 style synthetic state, vectorised numpy.  Returns dict of flat arrays + obs.
-
-    Map: Nf landmarks uniform in [-extent, extent]^2; true pose (0,0,0); particle poses = true pose +
-    N(0, diag(0.05^2, 0.05^2, (0.5deg)^2)); Pv = a fixed SPD matrix typical of 8 predict ticks;
-    landmark means = truth + N(0, 0.2^2 I); cov = Gz R Gz^T of addFeature (core.cpp:498-500).
-    """
-    rng = np.random.default_rng(seed)
-    nf_cap = nf_cap or Nf
-    lm = rng.uniform(-extent, extent, (Nf, 2)).astype(np.float32)
-    xv = np.zeros((3, P), np.float32)
-    xv[0] = rng.normal(0, 0.05, P)
-    xv[1] = rng.normal(0, 0.05, P)
-    xv[2] = rng.normal(0, 0.5 * np.pi / 180, P)
-    A = np.array([[0.02, 0.001, 0.0], [0.001, 0.03, 0.002], [0.0, 0.002, 0.004]], np.float64)
-    Pv0 = (A @ A.T + 1e-6 * np.eye(3)).astype(np.float32)
-    Pv = np.repeat(Pv0.reshape(9, 1), P, axis=1).astype(np.float32)
-    Pv *= (1.0 + 0.1 * rng.random((1, P), np.float32))
-    w = np.full(P, np.float32(1.0) / np.float32(P), np.float32)
-    lm_mean = np.empty((nf_cap, P, 2), np.float32)
-    lm_cov = np.empty((nf_cap, P, 4), np.float32)
-    R = R_DEFAULT
-    for l in range(Nf):
-        lm_mean[l] = lm[l] + rng.normal(0, 0.2, (P, 2)).astype(np.float32)
-        r = float(np.hypot(*lm[l]))
-        b = float(np.arctan2(lm[l, 1], lm[l, 0]))
-        Gz = np.array([[np.cos(b), -r * np.sin(b)], [np.sin(b), r * np.cos(b)]])
-        C = Gz @ R.astype(np.float64) @ Gz.T
-        lm_cov[l] = np.array([C[0, 0], C[1, 0], C[0, 1], C[1, 1]], np.float32)
-    lm_mean[Nf:] = 0
-    lm_cov[Nf:] = 0
-    order = np.argsort(np.hypot(lm[:, 0], lm[:, 1]))[:K]
-    idf = order.astype(np.int32)
-    zf = np.stack([np.hypot(lm[order, 0], lm[order, 1]) + rng.normal(0, 0.1, K),
-                   np.arctan2(lm[order, 1], lm[order, 0]) + rng.normal(0, np.pi / 180, K)], 1).astype(np.float32)
-    return dict(xv=xv, Pv=Pv, w=w, lm_mean=lm_mean, lm_cov=lm_cov, zf=zf, idf=idf, lm=lm, R=R)
+from slam_b200.synthetic import SYNTH_SIGMA_B, SYNTH_SIGMA_R, synthetic_state  # noqa: E402,F401  (shared with bench.py)

@@ -1,0 +1,279 @@
+"""GPU (B200): the CUDA path, called through the C ABI, against the oracle and the reference's golden vectors.
+
+Bit-exact: resample indices (keep[]), the resample decision, nEff and normalised weights (integer / pure fp32
+add-divide work).  Continuous state (poses, landmark means, covariances): 1e-4 norm-relative per object
+(BASELINE.json).  Unnormalised weights multiply likelihoods whose exponent cancels ~3 digits (z - zp), so one ulp of
+atan2f is worth ~1e-5 of weight per observation and compounds until the next resample: weights get 5e-4, the same
+bound tests/test_oracle_vs_ref.py needs between the oracle and the reference itself.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from replay import compare_states, load_golden, make_records, snapshot
+from scenario import Q_DEFAULT, R_DEFAULT, SIGMA_PHI, WHEELBASE, per_object_relerr, synthetic_state
+
+pytestmark = pytest.mark.gpu
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+TOL = 1e-4
+TOL_W = 5e-4
+
+
+@pytest.fixture(scope="module")
+def sb():
+    import slam_b200
+    slam_b200.build()
+    return slam_b200
+
+
+def test_compute_jacobians_record_matches_reference_kat(sb):
+    z = np.load(os.path.join(G, "jacobians_kat.npz"))
+    n = int(z["n"])
+    for rec, out in zip(z["rec"], z["out"]):
+        got = sb.compute_jacobians(rec, n).reshape(n, 16)
+        want = out.reshape(n, 16)
+        for a, b in zip(got, want):
+            assert per_object_relerr(a[0:1], b[0:1], None) <= 1e-6          # range
+            assert abs(a[1] - b[1]) <= 1e-6                                   # bearing
+            for sl in (slice(2, 6), slice(6, 12), slice(12, 16)):             # Hf, Hv, Sf
+                assert per_object_relerr(a[sl], b[sl], None) <= TOL
+
+
+@pytest.mark.parametrize("N", [100, 1000, 5000])
+def test_resample_indices_bit_exact_vs_reference_kat(sb, N):
+    from gpu_util import make_backend
+    z = np.load(os.path.join(G, "resample_kat.npz"))
+    f = make_backend(2, N, 4, n_effective=0)  # n_effective 0: never gathers, indices only
+    for trial in range(2):
+        w = z["w_%d_%d" % (N, trial)]
+        unif = z["ints_%d_%d" % (N, trial)] / float(2147483647)
+        f.upload(w=w)
+        keep, neff, did = f.resample(unif, want_keep=True)
+        assert np.array_equal(keep, z["keep_%d_%d" % (N, trial)])
+        assert neff == z["neff_%d_%d" % (N, trial)]
+        assert not did
+
+
+@pytest.mark.parametrize("N", [1, 31, 100, 1000, 1024, 1025, 4096, 5000, 100000, 1 << 20])
+def test_resample_blocked_bit_exact_vs_oracle(sb, oracle, N):
+    from gpu_util import make_backend
+    f = make_backend(2, N, 4, n_effective=0, scan_mode=sb.SCAN_BLOCKED)
+    rng = np.random.default_rng(N)
+    for trial in range(3):
+        w = (rng.random(N) ** (1 + 6 * trial)).astype(np.float32) + np.float32(1e-30)
+        if trial == 2:
+            w[rng.integers(0, N, size=max(1, N // 10))] = 0  # dead particles
+            w[0] = 1
+        unif = rng.integers(0, 2147483647, size=N) / float(2147483647)
+        f.upload(w=w)
+        keep, neff, did = f.resample(unif, want_keep=True)
+        wn, keep_o, neff_o = oracle.resample_indices(w, unif, scan_mode=1)
+        assert np.array_equal(f.download(landmarks=False)["w"], wn)
+        assert neff == neff_o
+        assert np.array_equal(keep, keep_o), (N, trial, int((keep != keep_o).sum()))
+
+
+def test_resample_blocked_equals_sequential_on_exact_weights(sb, oracle):
+    """Weights that are multiples of 2^-24 summing to <= 1 add exactly in any order: the blocked tree
+    must then give the SAME keep[] as the reference's sequential order."""
+    from gpu_util import make_backend
+    N = 1 << 16
+    rng = np.random.default_rng(3)
+    q = rng.multinomial(1 << 24, np.ones(N) / N).astype(np.float64)
+    w = (q / (1 << 24)).astype(np.float32)
+    assert float(np.sum(w.astype(np.float64))) == 1.0
+    unif = rng.integers(0, 2147483647, size=N) / float(2147483647)
+    f = make_backend(2, N, 4, n_effective=0, scan_mode=sb.SCAN_BLOCKED)
+    f.upload(w=w)
+    keep, neff, _ = f.resample(unif, want_keep=True)
+    _, keep_seq, _ = oracle.resample_indices(w, unif, scan_mode=0)
+    assert np.array_equal(keep, keep_seq)
+
+
+def _drive(sb, oracle, method, heading, noise, P, scan_mode, n_observe=8, max_obs=6):
+    from gpu_util import gpu_snapshot, make_backend
+    from oracle.pyoracle import State
+    cap = 40
+    recs = make_records(oracle, 70 + method, method, P, n_observe=n_observe, use_heading=heading, predict_noise=noise,
+                        max_obs=max_obs)
+    f = make_backend(method, P, cap, use_heading=heading, n_effective=int(0.75 * P), scan_mode=scan_mode)
+    s = State(P, cap)
+    n_resampled = 0
+    for i, r in enumerate(recs):
+        if r["kind"] == "predict":
+            oracle.predict(method, s, r["V"], r["G"], Q_DEFAULT, r["dt"], r["phi_true"], WHEELBASE, SIGMA_PHI,
+                           r["use_heading"], r["gauss"])
+            f.predict(r["V"], r["G"], Q_DEFAULT, r["dt"], r["phi_true"], r["gauss"])
+        else:
+            oracle.update_particles(method, s, r["zf"], r["idf"], r["zn"], R_DEFAULT, r["gauss"])
+            f.update_particles(r["zf"], r["idf"], r["zn"], R_DEFAULT, r["gauss"] if method == 2 else None)
+            g = gpu_snapshot(f)
+            compare_states(g, snapshot(s), TOL, "record %d before resample" % i, tol_w=TOL_W)
+            # continue from the device's weights so that both sides resample the same numbers: indices, nEff and the
+            # decision must then agree bit for bit
+            s.w[:] = g["w"]
+            keep, neff, did = f.resample(r["unif"], want_keep=True)
+            keep_o, neff_o, did_o = oracle.resample(s, r["unif"], r["n_effective"], r["do_resample"],
+                                                    scan_mode=1 if scan_mode == sb.SCAN_BLOCKED else 0)
+            assert np.array_equal(keep, keep_o), "record %d keep[]" % i
+            assert neff == neff_o and did == did_o
+            n_resampled += did
+        compare_states(gpu_snapshot(f), snapshot(s), TOL, "record %d (%s)" % (i, r["kind"]), tol_w=TOL_W)
+    return n_resampled
+
+
+@pytest.mark.parametrize("method,heading,noise", [(1, False, True), (1, True, True), (2, True, False), (2, False, True)])
+def test_drive_reference_order_p100(sb, oracle, method, heading, noise):
+    """The reference's own size (NPARTICLES 100), reference summation order."""
+    assert _drive(sb, oracle, method, heading, noise, 100, sb.SCAN_REFERENCE) > 0
+
+
+@pytest.mark.parametrize("method", [1, 2])
+def test_drive_blocked_order_ragged_p(sb, oracle, method):
+    """P not a multiple of the CTA / scan-block size, blocked summation order."""
+    assert _drive(sb, oracle, method, True, method == 1, 3000, sb.SCAN_BLOCKED, n_observe=6) > 0
+
+
+@pytest.mark.parametrize("method", [1, 2])
+def test_one_step_against_reference_golden(sb, method):
+    """Each record applied to the REFERENCE's previous output state and compared with the reference's next output
+    (tests/golden/drive_fs*_p100.npz, produced by the unmodified reference)."""
+    from gpu_util import gpu_snapshot, make_backend, upload_snapshot
+    recs, outs, meta = load_golden(os.path.join(G, "drive_fs%d_p100.npz" % method))
+    P, cap = int(meta["P"]), int(meta["nf_cap"])
+    f = make_backend(method, P, cap, use_heading=True, n_effective=int(0.75 * P), scan_mode=sb.SCAN_REFERENCE)
+    checked = 0
+    for i, r in enumerate(recs):
+        if r["kind"] == "predict":
+            f.predict(r["V"], r["G"], Q_DEFAULT, r["dt"], r["phi_true"], r["gauss"])
+        else:
+            f.update(r["zf"], r["idf"], r["zn"], R_DEFAULT, r["gauss"] if method == 2 else None, r["unif"])
+        compare_states(gpu_snapshot(f), outs[i], TOL, "record %d (%s)" % (i, r["kind"]), tol_w=TOL_W)
+        upload_snapshot(f, outs[i])
+        checked += 1
+    assert checked == len(recs)
+
+
+def test_synthetic_k32_update_and_estimate(sb, oracle):
+    """cfg-4 shaped update (K = 32 observed landmarks of Nf = 96) at a ragged particle count."""
+    from gpu_util import gpu_snapshot, make_backend, upload_state
+    from oracle.pyoracle import State
+    P, Nf, K = 5000, 96, 32
+    d = synthetic_state(P, Nf, K, seed=5)
+    rng = np.random.default_rng(11)
+    gauss = rng.standard_normal((3, P)).astype(np.float32)
+    s = State(P, Nf)
+    s.xv[:], s.Pv[:], s.w[:], s.lm_mean[:], s.lm_cov[:] = d["xv"], d["Pv"], d["w"], d["lm_mean"], d["lm_cov"]
+    s.Nf = Nf
+    f = make_backend(2, P, Nf, scan_mode=sb.SCAN_BLOCKED)
+    upload_state(f, s)
+    jac = f.compute_jacobians_batch(d["idf"][:3], d["R"])
+    for p in (0, 17, P - 1):  # batched computeJacobians against the oracle's record form
+        rec = [*s.xv[:, p], d["R"][0, 0], d["R"][1, 0], d["R"][0, 1], d["R"][1, 1]]
+        for l in d["idf"][:3]:
+            rec += [*s.lm_mean[l, p], *s.lm_cov[l, p]]
+        want = oracle.compute_jacobians(np.array(rec, np.float32), 3).reshape(3, 16)
+        for a, b in zip(jac[:, p], want):
+            assert abs(a[1] - b[1]) <= 1e-6 and per_object_relerr(a[[0]], b[[0]], None) <= 1e-6
+            for sl in (slice(2, 6), slice(6, 12), slice(12, 16)):
+                assert per_object_relerr(a[sl], b[sl], None) <= TOL
+    oracle.update_particles(2, s, d["zf"], d["idf"], np.zeros((0, 2), np.float32), d["R"], gauss)
+    f.update_particles(d["zf"], d["idf"], np.zeros((0, 2), np.float32), d["R"], gauss)
+    g = gpu_snapshot(f)
+    errs = compare_states(g, snapshot(s), TOL, "K=32 update", tol_w=1e9)
+    wa, wb = g["w"] / g["w"].sum(), s.w / s.w.sum()
+    assert np.abs(wa - wb).max() <= 2e-3 * wb.max(), errs  # 32 likelihood factors, see module docstring
+    ex = oracle.estimate(s)
+    s.xv[:], s.w[:] = g["xv"], g["w"]
+    ex = oracle.estimate(s)
+    gx = f.estimate()
+    assert abs(gx[0] - ex[0]) <= 1e-9 + 1e-12 * abs(ex[0]) and abs(gx[1] - ex[1]) <= 1e-9 and gx[2] == ex[2]
+    xv_d, lm_d = f.download_decimated(7, landmarks=True)
+    assert np.array_equal(xv_d, g["xv"][:, ::7]) and np.array_equal(lm_d, g["lm_mean"][:, ::7])
+
+
+def test_resample_gather_moves_whole_map(sb, oracle):
+    """Forced resample: poses and every landmark row follow keep[] exactly (a copy: bit-exact), across more rows
+    than the ring's spare rows so that several batches run, and twice so that the ring wraps."""
+    from gpu_util import gpu_snapshot, make_backend, upload_state
+    from oracle.pyoracle import State
+    P, Nf = 3000, 23
+    rng = np.random.default_rng(2)
+    s = State(P, Nf + 2)
+    s.xv[:] = rng.standard_normal((3, P))
+    s.Pv[:] = rng.standard_normal((9, P))
+    s.lm_mean[:Nf] = rng.standard_normal((Nf, P, 2))
+    s.lm_cov[:Nf] = rng.standard_normal((Nf, P, 4))
+    s.Nf = Nf
+    f = make_backend(2, P, Nf + 2, n_effective=P + 1, scan_mode=sb.SCAN_BLOCKED, spare_rows=5)
+    for rnd in range(3):
+        s.w[:] = rng.random(P).astype(np.float32) ** 4
+        upload_state(f, s) if rnd == 0 else f.upload(w=s.w)
+        unif = rng.random(P)
+        keep, neff, did = f.resample(unif, want_keep=True)
+        keep_o, neff_o, did_o = oracle.resample(s, unif, P + 1, True, scan_mode=1)
+        assert did and did_o and np.array_equal(keep, keep_o) and neff == neff_o
+        g = gpu_snapshot(f)
+        for k in ("xv", "Pv", "w"):
+            assert np.array_equal(g[k], getattr(s, k)), (rnd, k)
+        assert np.array_equal(g["lm_mean"], s.lm_mean[:Nf]) and np.array_equal(g["lm_cov"], s.lm_cov[:Nf])
+
+
+def test_error_paths(sb):
+    from gpu_util import make_backend
+    f = make_backend(2, 128, 2)
+    g = np.zeros((3, 128), np.float32)
+    f.update_particles(np.zeros((0, 2)), np.zeros(0, np.int32), [[5.0, 0.1], [6.0, -0.2]], R_DEFAULT, g)
+    assert f.Nf == 2
+    with pytest.raises(sb.SlamGpuError) as e:  # capacity
+        f.update_particles(np.zeros((0, 2)), np.zeros(0, np.int32), [[5.0, 0.1]], R_DEFAULT, g)
+    assert e.value.code == -5
+    with pytest.raises(sb.SlamGpuError):  # the same landmark twice
+        f.update_particles([[5.0, 0.1], [5.0, 0.1]], [1, 1], np.zeros((0, 2)), R_DEFAULT, g)
+    with pytest.raises(sb.SlamGpuError):  # row that does not exist
+        f.update_particles([[5.0, 0.1]], [2], np.zeros((0, 2)), R_DEFAULT, g)
+    with pytest.raises(sb.SlamGpuError):  # FastSLAM2 needs its Gaussians
+        f.update_particles([[5.0, 0.1]], [0], np.zeros((0, 2)), R_DEFAULT, None)
+
+
+def test_full_size_slices_1m_particles(sb, oracle):
+    """BASELINE.json cfg-4 particle count (2^20) with K = 32: the device result on the first / middle / last 2048
+    particles equals the oracle run on those particles alone (particles are independent in update_particles), and a
+    forced resample of the whole set keeps the checksum-of-rows property: every output row is the input row permuted
+    by keep[]."""
+    from gpu_util import make_backend
+    from oracle.pyoracle import State
+    P, Nf, K, n = 1 << 20, 40, 32, 2048
+    d = synthetic_state(n * 3, Nf, K, seed=8)
+    rng = np.random.default_rng(12)
+    reps = P // (3 * n) + 1
+    sel = np.concatenate([np.arange(0, n), np.arange(P // 2, P // 2 + n), np.arange(P - n, P)])
+
+    def tile(a, axis):  # fill 2^20 particles by tiling the 6144 generated ones; the checked slices get distinct data
+        return np.ascontiguousarray(np.take(np.concatenate([a] * reps, axis=axis), np.arange(P), axis=axis))
+
+    full = dict(xv=tile(d["xv"], 1), Pv=tile(d["Pv"], 1), lm_mean=tile(d["lm_mean"], 1), lm_cov=tile(d["lm_cov"], 1))
+    gauss = rng.standard_normal((3, P)).astype(np.float32)
+    w = np.full(P, np.float32(1.0 / P), np.float32)
+    f = make_backend(2, P, Nf, n_effective=P + 1, scan_mode=sb.SCAN_BLOCKED)
+    f.upload(full["xv"], full["Pv"], w, full["lm_mean"], full["lm_cov"], Nf)
+    f.update_particles(d["zf"], d["idf"], np.zeros((0, 2), np.float32), d["R"], gauss)
+    g = f.download()
+    s = State(3 * n, Nf)
+    s.xv[:], s.Pv[:], s.w[:] = full["xv"][:, sel], full["Pv"][:, sel], w[sel]
+    s.lm_mean[:], s.lm_cov[:], s.Nf = full["lm_mean"][:, sel], full["lm_cov"][:, sel], Nf
+    oracle.update_particles(2, s, d["zf"], d["idf"], np.zeros((0, 2), np.float32), d["R"],
+                            np.ascontiguousarray(gauss[:, sel]))
+    sub = dict(xv=g["xv"][:, sel], Pv=g["Pv"][:, sel], w=g["w"][sel], lm_mean=g["lm_mean"][:, sel],
+               lm_cov=g["lm_cov"][:, sel], Nf=Nf)
+    compare_states(sub, snapshot(s), TOL, "2^20 slices", tol_w=1e9)
+    assert np.abs(sub["w"] - s.w).max() <= 2e-3 * s.w.max()
+    unif = rng.random(P)
+    keep, neff, did = f.resample(unif, want_keep=True)
+    wn, keep_o, neff_o = oracle.resample_indices(g["w"], unif, scan_mode=1)
+    assert did and np.array_equal(keep, keep_o) and neff == neff_o
+    g2 = f.download()
+    assert np.array_equal(g2["xv"], g["xv"][:, keep]) and np.array_equal(g2["lm_cov"], g["lm_cov"][:, keep])
+    assert np.array_equal(g2["lm_mean"], g["lm_mean"][:, keep])
