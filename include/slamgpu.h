@@ -53,6 +53,13 @@ extern "C" {
 #define SLAMGPU_SCAN_REFERENCE 0
 #define SLAMGPU_SCAN_BLOCKED 1
 
+/* Arithmetic of the per-particle update kernels (same estimator, same quirks, different operation order):
+ * FAST           : information-form proposal, shared Cholesky factors, rsqrt / rcp (slam_math.cuh) — the default.
+ * REFERENCE_ORDER: the reference's own sequence of Eigen operations (llt().solve, PartialPivLU inverse, ...),
+ *                  IEEE division and square root; ~3.5x more instructions; for parity investigations. */
+#define SLAMGPU_MATH_FAST 0
+#define SLAMGPU_MATH_REFERENCE_ORDER 1
+
 typedef struct slamgpu slamgpu_t;
 
 typedef struct slamgpu_config {
@@ -67,7 +74,8 @@ typedef struct slamgpu_config {
     int32_t scan_mode;   /* SLAMGPU_SCAN_* */
     int32_t device;      /* CUDA device ordinal */
     int32_t spare_rows;  /* landmark rows kept free for the resample ring (0 = default) */
-    int32_t reserved[4];
+    int32_t math_mode;   /* SLAMGPU_MATH_* */
+    int32_t reserved[3];
 } slamgpu_config;
 
 const char *slamgpu_last_error(void);
@@ -90,7 +98,8 @@ void *slamgpu_host_alloc(uint64_t bytes);
 void slamgpu_host_free(void *p);
 
 /* Whole-state transfer in the flat layout above (vector<Particle> <-> device).  Any pointer may be NULL
- * to skip that field.  Nf rows of lm_* are moved. */
+ * to skip that field.  Nf rows of lm_* are moved and Nf becomes the landmark count; upload with Nf < 0 leaves the
+ * landmark count as it is (e.g. to replace only the weights). */
 int slamgpu_upload_particles(slamgpu_t *h, const float *xv, const float *Pv, const float *w, const float *lm_mean,
                              const float *lm_cov, int32_t Nf);
 int slamgpu_download_particles(slamgpu_t *h, float *xv, float *Pv, float *w, float *lm_mean, float *lm_cov,

@@ -22,7 +22,7 @@ class Config(C.Structure):
     _fields_ = [("n_particles", C.c_int64), ("nf_cap", C.c_int32), ("method", C.c_int32), ("wheel_base", C.c_float),
                 ("sigma_phi", C.c_float), ("n_effective", C.c_int32), ("use_heading", C.c_int32),
                 ("do_resample", C.c_int32), ("scan_mode", C.c_int32), ("device", C.c_int32), ("spare_rows", C.c_int32),
-                ("reserved", C.c_int32 * 4)]
+                ("math_mode", C.c_int32), ("reserved", C.c_int32 * 3)]
 
 
 _lib = None

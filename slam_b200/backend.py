@@ -17,6 +17,7 @@ from . import _lib
 
 FASTSLAM1, FASTSLAM2 = 1, 2
 SCAN_REFERENCE, SCAN_BLOCKED = 0, 1
+MATH_FAST, MATH_REFERENCE_ORDER = 0, 1
 T_PREDICT, T_UPDATE, T_ADDFEAT, T_WEIGHTS, T_GATHER, T_ESTIMATE = range(6)
 T_NAMES = ["predict", "update", "add_feature", "weights", "gather", "estimate"]
 
@@ -39,7 +40,7 @@ class FastSLAM:
     """One FastSLAM1/FastSLAM2 particle set on one CUDA device."""
 
     def __init__(self, method, n_particles, nf_cap, wheel_base=4.0, sigma_phi=0.0, n_effective=None, use_heading=False,
-                 resample=True, scan_mode=SCAN_BLOCKED, device=0, spare_rows=0):
+                 resample=True, scan_mode=SCAN_BLOCKED, device=0, spare_rows=0, math_mode=MATH_FAST):
         self._L = _lib.load()
         self._h = C.c_void_p()
         self.P = int(n_particles)
@@ -57,6 +58,7 @@ class FastSLAM:
         cfg.scan_mode = scan_mode
         cfg.device = device
         cfg.spare_rows = spare_rows
+        cfg.math_mode = math_mode
         self._check(self._L.slamgpu_create(C.byref(cfg), C.byref(self._h)))
 
     # -- plumbing ---------------------------------------------------------------
@@ -103,7 +105,7 @@ class FastSLAM:
         return bytes(buf)
 
     # -- state ----------------------------------------------------------------------
-    def upload(self, xv=None, Pv=None, w=None, lm_mean=None, lm_cov=None, Nf=0):
+    def upload(self, xv=None, Pv=None, w=None, lm_mean=None, lm_cov=None, Nf=-1):
         xv, Pv, w, lm_mean, lm_cov = map(_f32, (xv, Pv, w, lm_mean, lm_cov))
         self._check(self._L.slamgpu_upload_particles(self._h, _ptr(xv), _ptr(Pv), _ptr(w), _ptr(lm_mean),
                                                      _ptr(lm_cov), int(Nf)))

@@ -187,6 +187,8 @@ extern "C" int slamgpu_create(const slamgpu_config *cfg, slamgpu_t **out) {
         return slam_fail(SLAMGPU_EINVAL, "method must be SLAMGPU_FASTSLAM1 or SLAMGPU_FASTSLAM2");
     if (cfg->scan_mode != SLAMGPU_SCAN_REFERENCE && cfg->scan_mode != SLAMGPU_SCAN_BLOCKED)
         return slam_fail(SLAMGPU_EINVAL, "scan_mode must be SLAMGPU_SCAN_REFERENCE or SLAMGPU_SCAN_BLOCKED");
+    if (cfg->math_mode != SLAMGPU_MATH_FAST && cfg->math_mode != SLAMGPU_MATH_REFERENCE_ORDER)
+        return slam_fail(SLAMGPU_EINVAL, "math_mode must be SLAMGPU_MATH_FAST or SLAMGPU_MATH_REFERENCE_ORDER");
     slamgpu *h = new slamgpu();
     h->cfg = *cfg;
     h->P = h->Pg = (size_t) cfg->n_particles;
@@ -227,7 +229,8 @@ extern "C" int64_t slamgpu_launch_count(slamgpu_t *h) { return h ? h->launches :
 extern "C" int slamgpu_upload_particles(slamgpu_t *h, const float *xv, const float *Pv, const float *w,
                                         const float *lm_mean, const float *lm_cov, int32_t Nf) {
     if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
-    if (Nf < 0 || Nf > h->nf_cap) return slam_fail(SLAMGPU_ECAP, "Nf exceeds nf_cap");
+    if (Nf > h->nf_cap) return slam_fail(SLAMGPU_ECAP, "Nf exceeds nf_cap");
+    if (Nf < 0) Nf = (lm_mean || lm_cov) ? h->Nf : -1;  // negative: keep the current landmark count
     CU(cudaSetDevice(h->cfg.device));
     const size_t P = h->P;
     PoseSoA s = h->soa(h->cur);
@@ -243,7 +246,7 @@ extern "C" int slamgpu_upload_particles(slamgpu_t *h, const float *xv, const flo
             CU(cudaMemcpyAsync(h->lm_cov + row * P, lm_cov + (size_t) l * P * 4, sizeof(float4) * P,
                                cudaMemcpyHostToDevice, h->stream));
     }
-    h->Nf = Nf;
+    if (Nf >= 0) h->Nf = Nf;
     CU(cudaStreamSynchronize(h->stream));
     return SLAMGPU_OK;
 }
@@ -420,8 +423,13 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
         const size_t smem = (sizeof(float2) + sizeof(int)) * K;
         TimedSpan sp;
         RET(span_begin(h, SLAMGPU_T_UPDATE, &sp));
-        if (fs2)
+        const bool fast = h->cfg.math_mode == SLAMGPU_MATH_FAST;
+        if (fs2 && fast)
+            k_fs2_update_fast<<<grid_for(P, 128), 128, smem, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, dg);
+        else if (fs2)
             k_fs2_update<<<grid_for(P, 128), 128, smem, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, dg);
+        else if (fast)
+            k_fs1_update_fast<<<grid_for(P, 256), 256, smem, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm);
         else
             k_fs1_update<<<grid_for(P, 256), 256, smem, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm);
         KCHECK();

@@ -148,6 +148,115 @@ __global__ void __launch_bounds__(128) k_fs2_update(PoseSoA s, MapRing m, size_t
     store_pose(s, P, p, xs, Z);
 }
 
+// K3 (fast formulation, SLAMGPU_MATH_FAST): same kernel structure, ~3.5x fewer instructions (slam_math.cuh).
+// A particle whose pose covariance is not numerically positive definite takes the reference-order routine, kept
+// out of line so that it costs the common path nothing but a branch.
+__device__ __noinline__ void fs2_update_particle_reference_order(PoseSoA s, MapRing m, size_t P, size_t p,
+                                                                 const float2 *sz, const int *srow, int K, float4 Rm,
+                                                                 const float *gauss) {
+    const float R[4] = {Rm.x, Rm.y, Rm.z, Rm.w};
+    float x[3], C[9], x0[3], C0[9];
+    load_pose(s, P, p, x, C);
+    for (int j = 0; j < 3; j++) x0[j] = x[j];
+    for (int j = 0; j < 9; j++) C0[j] = C[j];
+    const float g3[3] = {gauss[p], gauss[P + p], gauss[2 * P + p]};
+    float xf[2], Pf[4];
+    for (int i = 0; i < K; i++) {
+        lm_load(m, P, srow[i], p, xf, Pf);
+        const float z[2] = {sz[i].x, sz[i].y};
+        proposal_step(x, C, R, xf, Pf, z);
+    }
+    float xs[3];
+    multivariate_gauss<3>(x, C, g3, xs);
+    const float v1[3] = {x0[0] - xs[0], x0[1] - xs[1], trig_offset(x0[2] - xs[2])};
+    const float v2[3] = {x[0] - xs[0], x[1] - xs[1], trig_offset(x[2] - xs[2])};
+    const float prior = gauss_evaluate<3>(v1, C0);
+    const float prop = gauss_evaluate<3>(v2, C);
+    float like = 1.0f;
+    for (int i = 0; i < K; i++) {
+        lm_load(m, P, srow[i], p, xf, Pf);
+        const float z[2] = {sz[i].x, sz[i].y};
+        like = like * likelihood_and_feature_update(xs, R, xf, Pf, z);
+        lm_store(m, P, srow[i], p, xf, Pf);
+    }
+    s.w[p] = s.w[p] * like * prior / prop;
+    const float Z[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    store_pose(s, P, p, xs, Z);
+}
+
+__global__ void __launch_bounds__(128) k_fs2_update_fast(PoseSoA s, MapRing m, size_t P, ObsSet o, int K, float4 Rm,
+                                                         const float *__restrict__ gauss) {
+    float2 *sz;
+    int *srow;
+    stage_obs(o, K, sz, srow);
+    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    const float R[4] = {Rm.x, Rm.y, Rm.z, Rm.w};
+    float x[3], x0[3], C0[9], L0[6];
+    load_pose(s, P, p, x0, C0);
+    ProposalInfo pi;
+    if (!proposal_begin_fast(C0, L0, pi)) {
+        fs2_update_particle_reference_order(s, m, P, p, sz, srow, K, Rm, gauss);
+        return;
+    }
+#pragma unroll
+    for (int j = 0; j < 3; j++) x[j] = x0[j];
+    const float g3[3] = {gauss[p], gauss[P + p], gauss[2 * P + p]};
+    float wgt = s.w[p];
+
+    float xf[2], Pf[4], nxf[2], nPf[4];
+    lm_load(m, P, srow[0], p, nxf, nPf);
+    for (int i = 0; i < K; i++) {
+        xf[0] = nxf[0]; xf[1] = nxf[1];
+#pragma unroll
+        for (int j = 0; j < 4; j++) Pf[j] = nPf[j];
+        if (i + 1 < K) lm_load(m, P, srow[i + 1], p, nxf, nPf);
+        const float z[2] = {sz[i].x, sz[i].y};
+        proposal_step_fast(x, pi, R, xf, Pf, z);
+    }
+    float xs[3];
+    const float ratio = proposal_finish_fast(x0, L0, x, pi, g3, xs);
+
+    float like = 1.0f;
+    lm_load(m, P, srow[0], p, nxf, nPf);
+    for (int i = 0; i < K; i++) {
+        xf[0] = nxf[0]; xf[1] = nxf[1];
+#pragma unroll
+        for (int j = 0; j < 4; j++) Pf[j] = nPf[j];
+        if (i + 1 < K) lm_load(m, P, srow[i + 1], p, nxf, nPf);
+        const float z[2] = {sz[i].x, sz[i].y};
+        like = like * likelihood_and_feature_update_fast(xs, R, xf, Pf, z);
+        lm_store(m, P, srow[i], p, xf, Pf);
+    }
+    s.w[p] = wgt * like * ratio;
+    const float Z[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    store_pose(s, P, p, xs, Z);
+}
+
+__global__ void __launch_bounds__(256) k_fs1_update_fast(PoseSoA s, MapRing m, size_t P, ObsSet o, int K, float4 Rm) {
+    float2 *sz;
+    int *srow;
+    stage_obs(o, K, sz, srow);
+    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    const float R[4] = {Rm.x, Rm.y, Rm.z, Rm.w};
+    float x[3];
+    load_pose(s, P, p, x, nullptr);
+    float wt = 1.0f;
+    float xf[2], Pf[4], nxf[2], nPf[4];
+    lm_load(m, P, srow[0], p, nxf, nPf);
+    for (int i = 0; i < K; i++) {
+        xf[0] = nxf[0]; xf[1] = nxf[1];
+#pragma unroll
+        for (int j = 0; j < 4; j++) Pf[j] = nPf[j];
+        if (i + 1 < K) lm_load(m, P, srow[i + 1], p, nxf, nPf);
+        const float z[2] = {sz[i].x, sz[i].y};
+        wt = wt * likelihood_and_feature_update_fast(x, R, xf, Pf, z);
+        lm_store(m, P, srow[i], p, xf, Pf);
+    }
+    s.w[p] = s.w[p] * wt;
+}
+
 // K3'  FastSLAM1 per-particle update: computeWeight (fastslam1.cpp:91-118) + featureUpdate, one pass.
 __global__ void __launch_bounds__(256) k_fs1_update(PoseSoA s, MapRing m, size_t P, ObsSet o, int K, float4 Rm) {
     float2 *sz;
@@ -310,7 +419,7 @@ __global__ void __launch_bounds__(SLAM_SCAN_BLOCK) k_block_totals(const float *_
 // Steps B/D: the recursive part of the blocked scan over a totals array, by ONE CTA of 1024 threads, in place.
 // Handles n <= 1024*1024 totals (P <= 2^30): chunks of 1024 are scanned locally one after the other, the chunk
 // totals are scanned as one block (that is the recursion's last level), and added back.
-// blockIdx.x selects one of up to 3 independent arrays.  sum_out[blockIdx.x] = last element of the scan.
+// blockIdx.x selects one of up to 3 independent arrays.  sum_out[blockIdx.x] = blocked_sum of the level below.
 struct UpperArgs {
     float *arr[3];
     float *sum_out[3];
@@ -323,6 +432,8 @@ __global__ void __launch_bounds__(SLAM_SCAN_BLOCK) k_scan_upper(UpperArgs a) {
     float *x = a.arr[blockIdx.x];
     const int n = a.n;
     const int nchunk = (n + SLAM_SCAN_BLOCK - 1) / SLAM_SCAN_BLOCK;
+    // the SUM of the level below is the last element of ITS scan = scanned[n-2] + (unscanned) x[n-1]
+    const float orig_last = (threadIdx.x == 0) ? x[n - 1] : 0.0f;
     for (int c = 0; c < nchunk; c++) {
         const int i = c * SLAM_SCAN_BLOCK + threadIdx.x;
         const float v = (i < n) ? x[i] : (a.use_max ? -INFINITY : 0.0f);
@@ -344,7 +455,8 @@ __global__ void __launch_bounds__(SLAM_SCAN_BLOCK) k_scan_upper(UpperArgs a) {
         }
     }
     __syncthreads();
-    if (threadIdx.x == 0 && a.sum_out[blockIdx.x]) *a.sum_out[blockIdx.x] = x[n - 1];
+    if (threadIdx.x == 0 && a.sum_out[blockIdx.x])
+        *a.sum_out[blockIdx.x] = (n > 1) ? __fadd_rn(x[n - 2], orig_last) : orig_last;
 }
 
 // Step C: normalise (core.cpp:727-729 / 784-786: one quotient serves both), local CDF scan, totals of w and w^2.

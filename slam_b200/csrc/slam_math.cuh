@@ -397,4 +397,208 @@ SLAM_HD void fs1_weight_and_feature_update(const float *x, const float *R, float
     cholesky_update(xf, Pf, v, R, Hf);
 }
 
+
+// =============================================================================================================
+// FAST formulation (SLAMGPU_MATH_FAST): the same estimator with the arithmetic reorganised for instruction count.
+//
+// The reference-order functions above cost ~1000 SASS instructions per particle-landmark (ncu, profiles/): IEEE
+// divisions, a Jacobi-free but still explicit 3x3 inverse TWICE per observation, an LU inverse of S, separate
+// Cholesky factorisations for the likelihood and for the landmark EKF.  The forms below are algebraically identical
+// and keep every reference quirk that changes results (integer D/2 in the Gaussian normaliser, sin(G/wheelBase), Pv
+// zeroed after sampling, S symmetrised but P not), but:
+//   * sampleProposal runs in INFORMATION form: Lambda = Pv^-1 is carried across observations (the reference inverts Pv,
+//     adds Hv' Sf^-1 Hv and inverts back: inv(inv(A)) == A), the pose increment is one Cholesky SOLVE, and Pv itself
+//     is formed once per particle after the last observation (it is only needed for the pose sample and the proposal
+//     density);
+//   * Sf^-1 is the 2x2 adjugate / determinant; Cholesky factors use rsqrt (no division, no sqrt);
+//   * likelihoodGivenXv's factor and choleskyUpdate share ONE factorisation of the symmetrised S, and the landmark
+//     mean update reuses the whitened innovation (W*v == W1 * (L^-1 v)).
+// Differences from the reference are rounding-level (a few ulp per operation); tests bound them against the oracle
+// with the same tolerances as the reference-order path.
+// =============================================================================================================
+#if defined(__CUDA_ARCH__)
+#define SLAM_RSQRT(x) rsqrtf(x)
+#define SLAM_RCP(x) __fdividef(1.0f, (x))
+#define SLAM_EXP(x) __expf(x)
+#else
+#define SLAM_RSQRT(x) (1.0f / sqrtf(x))
+#define SLAM_RCP(x) (1.0f / (x))
+#define SLAM_EXP(x) expf(x)
+#endif
+
+#define SLAM_INV_TWO_PI 0.159154943f
+
+// computeJacobians (core.cpp:666-713) for one landmark: predicted observation, Hf and the symmetrised innovation
+// covariance S = Hf Pf Hf' + R as (s00, s10, s11).  Pf row-major, may be asymmetric.
+SLAM_HD void jacobian_fast(const float *xv, const float *R, const float *xf, const float *Pf, float *zp, float *Hf,
+                           float *S3) {
+    const float dx = xf[0] - xv[0];
+    const float dy = xf[1] - xv[1];
+    const float d2 = fmaf(dx, dx, dy * dy);
+    const float rd = SLAM_RSQRT(d2);
+    float d = d2 * rd;
+    d = fmaf(0.5f * rd, fmaf(-d, d, d2), d);  // one Newton step: the range innovation cancels ~3 digits
+    const float rd2 = rd * rd;
+    zp[0] = d;
+    zp[1] = trig_offset(atan2f(dy, dx) - xv[2]);
+    Hf[0] = dx * rd;
+    Hf[1] = dy * rd;
+    Hf[2] = -dy * rd2;
+    Hf[3] = dx * rd2;
+    const float t00 = fmaf(Hf[0], Pf[0], Hf[1] * Pf[2]), t01 = fmaf(Hf[0], Pf[1], Hf[1] * Pf[3]);
+    const float t10 = fmaf(Hf[2], Pf[0], Hf[3] * Pf[2]), t11 = fmaf(Hf[2], Pf[1], Hf[3] * Pf[3]);
+    const float s00 = fmaf(t00, Hf[0], t01 * Hf[1]) + R[0];
+    const float s01 = fmaf(t00, Hf[2], t01 * Hf[3]) + R[1];
+    const float s10 = fmaf(t10, Hf[0], t11 * Hf[1]) + R[2];
+    const float s11 = fmaf(t10, Hf[2], t11 * Hf[3]) + R[3];
+    S3[0] = s00;
+    S3[1] = 0.5f * (s01 + s10);
+    S3[2] = s11;
+}
+
+// Lower Cholesky factor of a symmetric 3x3 given as (a00, a10, a11, a20, a21, a22), in reciprocal-diagonal form:
+// L = {l00i, l10, l11i, l20, l21, l22i} with lXXi = 1 / L[X][X].
+SLAM_HD void chol3_rs(const float *a, float *L) {
+    L[0] = SLAM_RSQRT(a[0]);
+    L[1] = a[1] * L[0];
+    L[3] = a[3] * L[0];
+    L[2] = SLAM_RSQRT(fmaf(-L[1], L[1], a[2]));
+    L[4] = fmaf(-L[3], L[1], a[4]) * L[2];
+    L[5] = SLAM_RSQRT(fmaf(-L[4], L[4], fmaf(-L[3], L[3], a[5])));
+}
+// y = L^-1 b
+SLAM_HD void chol3_fwd(const float *L, const float *b, float *y) {
+    y[0] = b[0] * L[0];
+    y[1] = fmaf(-L[1], y[0], b[1]) * L[2];
+    y[2] = fmaf(-L[4], y[1], fmaf(-L[3], y[0], b[2])) * L[5];
+}
+// x = L^-T y
+SLAM_HD void chol3_bwd(const float *L, const float *y, float *x) {
+    x[2] = y[2] * L[5];
+    x[1] = fmaf(-L[4], x[2], y[1]) * L[2];
+    x[0] = fmaf(-L[3], x[2], fmaf(-L[1], x[1], y[0])) * L[0];
+}
+// (L L')^-1 as packed symmetric (c00, c10, c11, c20, c21, c22)
+SLAM_HD void chol3_inverse(const float *L, float *c) {
+    // M = L^-1 (lower): m00 = l00i, m10 = -l10 m00 l11i, m11 = l11i, m20 = -(l20 m00 + l21 m10) l22i,
+    // m21 = -l21 m11 l22i, m22 = l22i;  inverse = M' M
+    const float m00 = L[0], m11 = L[2], m22 = L[5];
+    const float m10 = -L[1] * m00 * m11;
+    const float m21 = -L[4] * m11 * m22;
+    const float m20 = -fmaf(L[3], m00, L[4] * m10) * m22;
+    c[0] = fmaf(m00, m00, fmaf(m10, m10, m20 * m20));
+    c[1] = fmaf(m10, m11, m20 * m21);
+    c[2] = fmaf(m11, m11, m21 * m21);
+    c[3] = m20 * m22;
+    c[4] = m21 * m22;
+    c[5] = m22 * m22;
+}
+
+// Pose-side state of the information-form proposal.
+struct ProposalInfo {
+    float lam[6];  // Lambda = Pv^-1, packed lower (00, 10, 11, 20, 21, 22)
+};
+
+// One observation of FastSLAM2::sampleProposal (fastslam2.cpp:314-350) in information form.
+SLAM_HD void proposal_step_fast(float *x, ProposalInfo &pi, const float *R, const float *xf, const float *Pf,
+                                const float *z) {
+    float zp[2], Hf[4], S[3];
+    jacobian_fast(x, R, xf, Pf, zp, Hf, S);
+    const float v0 = z[0] - zp[0], v1 = trig_offset(z[1] - zp[1]);
+    // G = S^-1 (symmetric): adjugate / det
+    const float rdet = SLAM_RCP(fmaf(S[0], S[2], -S[1] * S[1]));
+    const float g00 = S[2] * rdet, g01 = -S[1] * rdet, g11 = S[0] * rdet;
+    // rows of Hv are -(Hf0, Hf1, 0) and -(Hf2, Hf3, 1); the signs cancel in Hv' G Hv
+    const float t10 = fmaf(g00, Hf[0], g01 * Hf[2]), t11 = fmaf(g00, Hf[1], g01 * Hf[3]), t12 = g01;
+    const float t20 = fmaf(g01, Hf[0], g11 * Hf[2]), t21 = fmaf(g01, Hf[1], g11 * Hf[3]), t22 = g11;
+    pi.lam[0] += fmaf(Hf[0], t10, Hf[2] * t20);
+    pi.lam[1] += fmaf(Hf[1], t10, Hf[3] * t20);
+    pi.lam[2] += fmaf(Hf[1], t11, Hf[3] * t21);
+    pi.lam[3] += t20;
+    pi.lam[4] += t21;
+    pi.lam[5] += t22;
+    (void) t12;
+    // b = Hv' G v = -(h1 u0 + h2 u1), u = G v
+    const float u0 = fmaf(g00, v0, g01 * v1), u1 = fmaf(g01, v0, g11 * v1);
+    const float b[3] = {-fmaf(Hf[0], u0, Hf[2] * u1), -fmaf(Hf[1], u0, Hf[3] * u1), -u1};
+    float L[6], y[3], dxv[3];
+    chol3_rs(pi.lam, L);
+    chol3_fwd(L, b, y);
+    chol3_bwd(L, y, dxv);
+    x[0] += dxv[0];
+    x[1] += dxv[1];
+    x[2] += dxv[2];
+}
+
+// exp(-0.5*|L^-1 v|^2) / (2*pi * prod diag L) for a packed reciprocal-diagonal factor (gaussEvaluate with D = 3,
+// fastslam2.cpp:127-163: the normaliser is (2*pi)^(3/2 as int) = 2*pi).
+SLAM_HD float gauss3_from_factor(const float *L, const float *v) {
+    float nin[3];
+    chol3_fwd(L, v, nin);
+    const float E = -0.5f * fmaf(nin[0], nin[0], fmaf(nin[1], nin[1], nin[2] * nin[2]));
+    return SLAM_EXP(E) * (SLAM_INV_TWO_PI * L[0] * L[2] * L[5]);
+}
+
+// Per-particle prologue: factor Pv0 once; gives Lambda0 = Pv0^-1 and the factor for the prior density.
+// Returns false when Pv0 is not numerically positive definite (a pivot <= 0 or NaN): the caller then takes the
+// reference-order path, which reproduces what Eigen's LLT does with such a matrix.
+SLAM_HD bool proposal_begin_fast(const float *C0, float *L0, ProposalInfo &pi) {
+    const float a[6] = {C0[0], C0[3], C0[4], C0[6], C0[7], C0[8]};  // lower triangle, like Eigen's LLT
+    chol3_rs(a, L0);
+    chol3_inverse(L0, pi.lam);
+    const float t = L0[0] * L0[2] * L0[5];
+    return (L0[0] > 0.0f) && (L0[2] > 0.0f) && (L0[5] > 0.0f) && (t < 3.0e38f);  // false for NaN / inf
+}
+
+// Per-particle epilogue (fastslam2.cpp:352-367): Pv = Lambda^-1, pose sample xs = x + chol(Pv)*g, and the weight
+// factor prior/proposal.  Returns prior / proposal; xs out.
+SLAM_HD float proposal_finish_fast(const float *x0, const float *L0, const float *x, const ProposalInfo &pi,
+                                   const float *g, float *xs) {
+    float Ll[6], c[6], Lc[6];
+    chol3_rs(pi.lam, Ll);
+    chol3_inverse(Ll, c);  // Pv, packed lower
+    chol3_rs(c, Lc);       // its lower Cholesky factor (reciprocal diagonals)
+    const float l00 = c[0] * Lc[0], l11 = fmaf(-Lc[1], Lc[1], c[2]) * Lc[2],
+                l22 = fmaf(-Lc[4], Lc[4], fmaf(-Lc[3], Lc[3], c[5])) * Lc[5];  // diag = a * rsqrt(a)
+    xs[0] = l00 * g[0] + x[0];
+    xs[1] = fmaf(l11, g[1], Lc[1] * g[0]) + x[1];
+    xs[2] = fmaf(l22, g[2], fmaf(Lc[4], g[1], Lc[3] * g[0])) + x[2];
+    const float v1[3] = {x0[0] - xs[0], x0[1] - xs[1], trig_offset(x0[2] - xs[2])};
+    const float v2[3] = {x[0] - xs[0], x[1] - xs[1], trig_offset(x[2] - xs[2])};
+    const float prior = gauss3_from_factor(L0, v1);
+    const float prop = gauss3_from_factor(Lc, v2);
+    return prior * SLAM_RCP(prop);
+}
+
+// Pass 2 for one observation at the (sampled) pose: likelihood factor (likelihoodGivenXv, fastslam2.cpp:370-400, or
+// FastSLAM1::computeWeight's term, fastslam1.cpp:91-118 — the same density) and the landmark EKF
+// (featureUpdate -> choleskyUpdate, core.cpp:132-175,275-291), sharing one factorisation of S.
+SLAM_HD float likelihood_and_feature_update_fast(const float *xs, const float *R, float *xf, float *Pf,
+                                                 const float *z) {
+    float zp[2], Hf[4], S[3];
+    jacobian_fast(xs, R, xf, Pf, zp, Hf, S);
+    const float v0 = z[0] - zp[0], v1 = trig_offset(z[1] - zp[1]);
+    const float l00i = SLAM_RSQRT(S[0]);
+    const float l10 = S[1] * l00i;
+    const float l11i = SLAM_RSQRT(fmaf(-l10, l10, S[2]));
+    const float n0 = v0 * l00i;
+    const float n1 = fmaf(-l10, n0, v1) * l11i;
+    const float E = -0.5f * fmaf(n0, n0, n1 * n1);
+    const float like = SLAM_EXP(E) * (SLAM_INV_TWO_PI * l00i * l11i);
+    // PHt = Pf Hf'
+    const float p00 = fmaf(Pf[0], Hf[0], Pf[1] * Hf[1]), p01 = fmaf(Pf[0], Hf[2], Pf[1] * Hf[3]);
+    const float p10 = fmaf(Pf[2], Hf[0], Pf[3] * Hf[1]), p11 = fmaf(Pf[2], Hf[2], Pf[3] * Hf[3]);
+    // W1 = PHt * U^-1, U = L' = [l00 l10; 0 l11]
+    const float w00 = p00 * l00i, w10 = p10 * l00i;
+    const float w01 = fmaf(-w00, l10, p01) * l11i, w11 = fmaf(-w10, l10, p11) * l11i;
+    xf[0] += fmaf(w00, n0, w01 * n1);
+    xf[1] += fmaf(w10, n0, w11 * n1);
+    const float c01 = fmaf(w00, w10, w01 * w11);
+    Pf[0] -= fmaf(w00, w00, w01 * w01);
+    Pf[1] -= c01;
+    Pf[2] -= c01;
+    Pf[3] -= fmaf(w10, w10, w11 * w11);
+    return like;
+}
+
 }  // namespace slam

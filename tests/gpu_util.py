@@ -6,9 +6,10 @@ from scenario import SIGMA_PHI, WHEELBASE
 
 
 def make_backend(method, P, nf_cap, use_heading=True, n_effective=None, scan_mode=slam_b200.SCAN_REFERENCE,
-                 resample=True, spare_rows=0):
+                 resample=True, spare_rows=0, math_mode=slam_b200.MATH_FAST):
     return slam_b200.FastSLAM(method, P, nf_cap, wheel_base=WHEELBASE, sigma_phi=SIGMA_PHI, n_effective=n_effective,
-                              use_heading=use_heading, resample=resample, scan_mode=scan_mode, spare_rows=spare_rows)
+                              use_heading=use_heading, resample=resample, scan_mode=scan_mode, spare_rows=spare_rows,
+                              math_mode=math_mode)
 
 
 def upload_state(f, s):

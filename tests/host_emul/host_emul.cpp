@@ -126,4 +126,52 @@ int he_fs1_update_particles(long P, int Nf, float *xv, float *Pv, float *w, floa
     }
     return Nf + Kn;
 }
+
+int he_fs2_update_particles_fast(long P, int Nf, float *xv, float *Pv, float *w, float *lm_mean, float *lm_cov,
+                                 const float *zf, const int *idf, int K, const float *R, const float *gauss) {
+    for (long p = 0; p < P; p++) {
+        float x[3], C[9], x0[3];
+        for (int c = 0; c < 3; c++) x0[c] = x[c] = xv[c * P + p];
+        for (int j = 0; j < 9; j++) C[j] = Pv[j * P + p];
+        const float g3[3] = {gauss[p], gauss[P + p], gauss[2 * P + p]};
+        float L0[6];
+        ProposalInfo pi;
+        proposal_begin_fast(C, L0, pi);
+        for (int i = 0; i < K; i++) {
+            float xf[2], Pf[4];
+            lm_load(P, p, idf[i], lm_mean, lm_cov, xf, Pf);
+            proposal_step_fast(x, pi, R, xf, Pf, zf + 2 * i);
+        }
+        float xs[3];
+        const float ratio = proposal_finish_fast(x0, L0, x, pi, g3, xs);
+        float like = 1.0f;
+        for (int i = 0; i < K; i++) {
+            float xf[2], Pf[4];
+            lm_load(P, p, idf[i], lm_mean, lm_cov, xf, Pf);
+            like = like * likelihood_and_feature_update_fast(xs, R, xf, Pf, zf + 2 * i);
+            lm_store(P, p, idf[i], lm_mean, lm_cov, xf, Pf);
+        }
+        w[p] = w[p] * like * ratio;
+        for (int c = 0; c < 3; c++) xv[c * P + p] = xs[c];
+        for (int j = 0; j < 9; j++) Pv[j * P + p] = 0;
+    }
+    return Nf;
+}
+
+int he_fs1_update_particles_fast(long P, int Nf, float *xv, float *w, float *lm_mean, float *lm_cov, const float *zf,
+                                 const int *idf, int K, const float *R) {
+    for (long p = 0; p < P; p++) {
+        float x[3];
+        for (int c = 0; c < 3; c++) x[c] = xv[c * P + p];
+        float wt = 1.0f;
+        for (int i = 0; i < K; i++) {
+            float xf[2], Pf[4];
+            lm_load(P, p, idf[i], lm_mean, lm_cov, xf, Pf);
+            wt = wt * likelihood_and_feature_update_fast(x, R, xf, Pf, zf + 2 * i);
+            lm_store(P, p, idf[i], lm_mean, lm_cov, xf, Pf);
+        }
+        w[p] = w[p] * wt;
+    }
+    return Nf;
+}
 }
