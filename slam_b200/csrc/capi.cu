@@ -391,6 +391,7 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
     if (!h || !R) return slam_fail(SLAMGPU_EINVAL, "null argument");
     if (K < 0 || Kn < 0 || (K > 0 && (!zf || !idf)) || (Kn > 0 && !zn)) return slam_fail(SLAMGPU_EINVAL, "bad observation set");
     if (h->Nf + Kn > h->nf_cap) return slam_fail(SLAMGPU_ECAP, "landmark capacity (nf_cap) exceeded");
+    if (K > 2048 || Kn > 2048) return slam_fail(SLAMGPU_EINVAL, "at most 2048 observations per update (shared-memory staging)");
     CU(cudaSetDevice(h->cfg.device));
     std::vector<int> rows(std::max(K, Kn));
     if (K > 0) {
@@ -424,12 +425,13 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
         TimedSpan sp;
         RET(span_begin(h, SLAMGPU_T_UPDATE, &sp));
         const bool fast = h->cfg.math_mode == SLAMGPU_MATH_FAST;
+        const size_t smem_fast = SLAM_OBS_OFF_SMEM(K);
         if (fs2 && fast)
-            k_fs2_update_fast<<<grid_for(P, 128), 128, smem, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, dg);
+            k_fs2_update_fast<<<grid_for(P, 128), 128, smem_fast, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, dg);
         else if (fs2)
             k_fs2_update<<<grid_for(P, 128), 128, smem, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, dg);
         else if (fast)
-            k_fs1_update_fast<<<grid_for(P, 256), 256, smem, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm);
+            k_fs1_update_fast<<<grid_for(P, 256), 256, smem_fast, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm);
         else
             k_fs1_update<<<grid_for(P, 256), 256, smem, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm);
         KCHECK();

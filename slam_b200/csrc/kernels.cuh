@@ -148,12 +148,19 @@ __global__ void __launch_bounds__(128) k_fs2_update(PoseSoA s, MapRing m, size_t
     store_pose(s, P, p, xs, Z);
 }
 
+__device__ __forceinline__ void lm_load_at(const float2 *mp, const float4 *cp, float *xf, float *Pf) {
+    const float2 a = *mp;
+    const float4 c = *cp;
+    xf[0] = a.x; xf[1] = a.y;
+    Pf[0] = c.x; Pf[1] = c.z; Pf[2] = c.y; Pf[3] = c.w;
+}
+
 // K3 (fast formulation, SLAMGPU_MATH_FAST): same kernel structure, ~3.5x fewer instructions (slam_math.cuh).
 // A particle whose pose covariance is not numerically positive definite takes the reference-order routine, kept
 // out of line so that it costs the common path nothing but a branch.
 __device__ __noinline__ void fs2_update_particle_reference_order(PoseSoA s, MapRing m, size_t P, size_t p,
-                                                                 const float2 *sz, const int *srow, int K, float4 Rm,
-                                                                 const float *gauss) {
+                                                                 const float2 *sz, const unsigned long long *soff,
+                                                                 int K, float4 Rm, const float *gauss) {
     const float R[4] = {Rm.x, Rm.y, Rm.z, Rm.w};
     float x[3], C[9], x0[3], C0[9];
     load_pose(s, P, p, x, C);
@@ -162,7 +169,7 @@ __device__ __noinline__ void fs2_update_particle_reference_order(PoseSoA s, MapR
     const float g3[3] = {gauss[p], gauss[P + p], gauss[2 * P + p]};
     float xf[2], Pf[4];
     for (int i = 0; i < K; i++) {
-        lm_load(m, P, srow[i], p, xf, Pf);
+        lm_load_at(m.mean + soff[i] + p, m.cov + soff[i] + p, xf, Pf);
         const float z[2] = {sz[i].x, sz[i].y};
         proposal_step(x, C, R, xf, Pf, z);
     }
@@ -174,21 +181,36 @@ __device__ __noinline__ void fs2_update_particle_reference_order(PoseSoA s, MapR
     const float prop = gauss_evaluate<3>(v2, C);
     float like = 1.0f;
     for (int i = 0; i < K; i++) {
-        lm_load(m, P, srow[i], p, xf, Pf);
+        lm_load_at(m.mean + soff[i] + p, m.cov + soff[i] + p, xf, Pf);
         const float z[2] = {sz[i].x, sz[i].y};
         like = like * likelihood_and_feature_update(xs, R, xf, Pf, z);
-        lm_store(m, P, srow[i], p, xf, Pf);
+        __stcs(m.mean + soff[i] + p, make_float2(xf[0], xf[1]));
+        __stcs(m.cov + soff[i] + p, make_float4(Pf[0], Pf[2], Pf[1], Pf[3]));
     }
     s.w[p] = s.w[p] * like * prior / prop;
     const float Z[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
     store_pose(s, P, p, xs, Z);
 }
 
+// Observation staging for the fast kernels: z and the element offset row*P of each observed landmark row, padded by
+// one copy of the last entry so that the "next landmark" prefetch needs no branch.
+__device__ __forceinline__ void stage_obs_off(const ObsSet &o, int K, size_t P, float2 *&sz, unsigned long long *&soff) {
+    soff = reinterpret_cast<unsigned long long *>(slam_smem);
+    sz = reinterpret_cast<float2 *>(soff + (K + 1));
+    for (int i = threadIdx.x; i <= K; i += blockDim.x) {
+        const int j = min(i, K - 1);
+        sz[i] = o.z[j];
+        soff[i] = (unsigned long long) o.row[j] * (unsigned long long) P;
+    }
+    __syncthreads();
+}
+#define SLAM_OBS_OFF_SMEM(K) ((sizeof(unsigned long long) + sizeof(float2)) * ((K) + 1))
+
 __global__ void __launch_bounds__(128) k_fs2_update_fast(PoseSoA s, MapRing m, size_t P, ObsSet o, int K, float4 Rm,
                                                          const float *__restrict__ gauss) {
     float2 *sz;
-    int *srow;
-    stage_obs(o, K, sz, srow);
+    unsigned long long *soff;
+    stage_obs_off(o, K, P, sz, soff);
     const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= P) return;
     const float R[4] = {Rm.x, Rm.y, Rm.z, Rm.w};
@@ -196,37 +218,46 @@ __global__ void __launch_bounds__(128) k_fs2_update_fast(PoseSoA s, MapRing m, s
     load_pose(s, P, p, x0, C0);
     ProposalInfo pi;
     if (!proposal_begin_fast(C0, L0, pi)) {
-        fs2_update_particle_reference_order(s, m, P, p, sz, srow, K, Rm, gauss);
+        fs2_update_particle_reference_order(s, m, P, p, sz, soff, K, Rm, gauss);
         return;
     }
 #pragma unroll
     for (int j = 0; j < 3; j++) x[j] = x0[j];
     const float g3[3] = {gauss[p], gauss[P + p], gauss[2 * P + p]};
-    float wgt = s.w[p];
+    const float wgt = s.w[p];
+    float2 *const mean_p = m.mean + p;
+    float4 *const cov_p = m.cov + p;
 
+    // pass 1: proposal (read only), the next landmark is in flight while this one is processed
     float xf[2], Pf[4], nxf[2], nPf[4];
-    lm_load(m, P, srow[0], p, nxf, nPf);
+    lm_load_at(mean_p + soff[0], cov_p + soff[0], nxf, nPf);
     for (int i = 0; i < K; i++) {
         xf[0] = nxf[0]; xf[1] = nxf[1];
 #pragma unroll
         for (int j = 0; j < 4; j++) Pf[j] = nPf[j];
-        if (i + 1 < K) lm_load(m, P, srow[i + 1], p, nxf, nPf);
+        const unsigned long long noff = soff[i + 1];
+        lm_load_at(mean_p + noff, cov_p + noff, nxf, nPf);
         const float z[2] = {sz[i].x, sz[i].y};
         proposal_step_fast(x, pi, R, xf, Pf, z);
     }
     float xs[3];
     const float ratio = proposal_finish_fast(x0, L0, x, pi, g3, xs);
 
+    // pass 2: likelihood at the sampled pose + landmark EKF, written back in place
     float like = 1.0f;
-    lm_load(m, P, srow[0], p, nxf, nPf);
+    unsigned long long off = soff[0];
+    lm_load_at(mean_p + off, cov_p + off, nxf, nPf);
     for (int i = 0; i < K; i++) {
         xf[0] = nxf[0]; xf[1] = nxf[1];
 #pragma unroll
         for (int j = 0; j < 4; j++) Pf[j] = nPf[j];
-        if (i + 1 < K) lm_load(m, P, srow[i + 1], p, nxf, nPf);
+        const unsigned long long noff = soff[i + 1];
+        lm_load_at(mean_p + noff, cov_p + noff, nxf, nPf);  // i == K-1 re-reads row K-1 before its store: harmless
         const float z[2] = {sz[i].x, sz[i].y};
         like = like * likelihood_and_feature_update_fast(xs, R, xf, Pf, z);
-        lm_store(m, P, srow[i], p, xf, Pf);
+        __stcs(mean_p + off, make_float2(xf[0], xf[1]));
+        __stcs(cov_p + off, make_float4(Pf[0], Pf[2], Pf[1], Pf[3]));
+        off = noff;
     }
     s.w[p] = wgt * like * ratio;
     const float Z[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
@@ -235,24 +266,30 @@ __global__ void __launch_bounds__(128) k_fs2_update_fast(PoseSoA s, MapRing m, s
 
 __global__ void __launch_bounds__(256) k_fs1_update_fast(PoseSoA s, MapRing m, size_t P, ObsSet o, int K, float4 Rm) {
     float2 *sz;
-    int *srow;
-    stage_obs(o, K, sz, srow);
+    unsigned long long *soff;
+    stage_obs_off(o, K, P, sz, soff);
     const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= P) return;
     const float R[4] = {Rm.x, Rm.y, Rm.z, Rm.w};
     float x[3];
     load_pose(s, P, p, x, nullptr);
+    float2 *const mean_p = m.mean + p;
+    float4 *const cov_p = m.cov + p;
     float wt = 1.0f;
     float xf[2], Pf[4], nxf[2], nPf[4];
-    lm_load(m, P, srow[0], p, nxf, nPf);
+    unsigned long long off = soff[0];
+    lm_load_at(mean_p + off, cov_p + off, nxf, nPf);
     for (int i = 0; i < K; i++) {
         xf[0] = nxf[0]; xf[1] = nxf[1];
 #pragma unroll
         for (int j = 0; j < 4; j++) Pf[j] = nPf[j];
-        if (i + 1 < K) lm_load(m, P, srow[i + 1], p, nxf, nPf);
+        const unsigned long long noff = soff[i + 1];
+        lm_load_at(mean_p + noff, cov_p + noff, nxf, nPf);
         const float z[2] = {sz[i].x, sz[i].y};
         wt = wt * likelihood_and_feature_update_fast(x, R, xf, Pf, z);
-        lm_store(m, P, srow[i], p, xf, Pf);
+        __stcs(mean_p + off, make_float2(xf[0], xf[1]));
+        __stcs(cov_p + off, make_float4(Pf[0], Pf[2], Pf[1], Pf[3]));
+        off = noff;
     }
     s.w[p] = s.w[p] * wt;
 }

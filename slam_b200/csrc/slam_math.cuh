@@ -428,7 +428,37 @@ SLAM_HD void fs1_weight_and_feature_update(const float *x, const float *R, float
 
 #define SLAM_INV_TWO_PI 0.159154943f
 
-// computeJacobians (core.cpp:666-713) for one landmark: predicted observation, Hf and the symmetrised innovation
+// atan2 for the bearing prediction: octant reduction to a = min/max in [0,1], degree-8 minimax polynomial in a^2
+// (max |error| 1.1e-7 rad in fp32, about what atan2f's 2 ulp is worth at |angle| ~ pi/2..pi), ~24 instructions
+// instead of ~60 for atan2f + the reference's two-branch wrap.
+SLAM_HD float atan2_fast(float y, float x) {
+    const float ax = fabsf(x), ay = fabsf(y);
+    const float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
+    const float a = mn * SLAM_RCP(mx);
+    const float q = a * a;
+    float r = 0.0028340641874819994f;
+    r = fmaf(r, q, -0.016005029901862144f);
+    r = fmaf(r, q, 0.042587608098983765f);
+    r = fmaf(r, q, -0.07495445758104324f);
+    r = fmaf(r, q, 0.10636754333972931f);
+    r = fmaf(r, q, -0.14202570915222168f);
+    r = fmaf(r, q, 0.19992484152317047f);
+    r = fmaf(r, q, -0.3333306610584259f);
+    r = fmaf(r * q, a, a);
+    if (ay > ax) r = 1.57079637f - r;
+    if (x < 0.0f) r = 3.14159274f - r;
+    return copysignf(r, y);
+}
+
+// Wrap an angle difference into [-pi, pi] (trigonometricOffset's job, core.cpp:460-477) by one rounding to the
+// nearest multiple of 2*pi; identical to the reference whenever no wrap is needed.
+SLAM_HD float wrap_fast(float t) {
+    const float k = rintf(t * SLAM_INV_TWO_PI);
+    return fmaf(k, SLAM_TWO_PI_LO, fmaf(-k, SLAM_TWO_PI_HI, t));
+}
+
+// computeJacobians (core.cpp:666-713) for one landmark: predicted range zp[0], UNWRAPPED predicted bearing zp[1] =
+// atan2(dy,dx) - theta (the caller wraps the innovation once), Hf and the symmetrised innovation
 // covariance S = Hf Pf Hf' + R as (s00, s10, s11).  Pf row-major, may be asymmetric.
 SLAM_HD void jacobian_fast(const float *xv, const float *R, const float *xf, const float *Pf, float *zp, float *Hf,
                            float *S3) {
@@ -440,7 +470,7 @@ SLAM_HD void jacobian_fast(const float *xv, const float *R, const float *xf, con
     d = fmaf(0.5f * rd, fmaf(-d, d, d2), d);  // one Newton step: the range innovation cancels ~3 digits
     const float rd2 = rd * rd;
     zp[0] = d;
-    zp[1] = trig_offset(atan2f(dy, dx) - xv[2]);
+    zp[1] = atan2_fast(dy, dx) - xv[2];
     Hf[0] = dx * rd;
     Hf[1] = dy * rd;
     Hf[2] = -dy * rd2;
@@ -504,7 +534,7 @@ SLAM_HD void proposal_step_fast(float *x, ProposalInfo &pi, const float *R, cons
                                 const float *z) {
     float zp[2], Hf[4], S[3];
     jacobian_fast(x, R, xf, Pf, zp, Hf, S);
-    const float v0 = z[0] - zp[0], v1 = trig_offset(z[1] - zp[1]);
+    const float v0 = z[0] - zp[0], v1 = wrap_fast(z[1] - zp[1]);
     // G = S^-1 (symmetric): adjugate / det
     const float rdet = SLAM_RCP(fmaf(S[0], S[2], -S[1] * S[1]));
     const float g00 = S[2] * rdet, g01 = -S[1] * rdet, g11 = S[0] * rdet;
@@ -577,7 +607,7 @@ SLAM_HD float likelihood_and_feature_update_fast(const float *xs, const float *R
                                                  const float *z) {
     float zp[2], Hf[4], S[3];
     jacobian_fast(xs, R, xf, Pf, zp, Hf, S);
-    const float v0 = z[0] - zp[0], v1 = trig_offset(z[1] - zp[1]);
+    const float v0 = z[0] - zp[0], v1 = wrap_fast(z[1] - zp[1]);
     const float l00i = SLAM_RSQRT(S[0]);
     const float l10 = S[1] * l00i;
     const float l11i = SLAM_RSQRT(fmaf(-l10, l10, S[2]));
