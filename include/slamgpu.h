@@ -73,9 +73,10 @@ typedef struct slamgpu_config {
     int32_t do_resample; /* SWITCH_RESAMPLE */
     int32_t scan_mode;   /* SLAMGPU_SCAN_* */
     int32_t device;      /* CUDA device ordinal */
-    int32_t spare_rows;  /* landmark rows kept free for the resample ring (0 = default) */
+    int32_t spare_rows;  /* free physical landmark rows for deferred gathers (0 = default: min(64, nf_cap)) */
     int32_t math_mode;   /* SLAMGPU_MATH_* */
-    int32_t reserved[3];
+    int32_t log_epochs;  /* resamples whose keep[] is retained for deferred map gathers (0 = default 64) */
+    int32_t reserved[2];
 } slamgpu_config;
 
 const char *slamgpu_last_error(void);
@@ -167,6 +168,12 @@ int slamgpu_timing_enable(slamgpu_t *h, int32_t on);
 /* Sums since the last reset; synchronises the stream.  launches = kernel launches of that family. */
 int slamgpu_timing_read(slamgpu_t *h, int32_t which, double *total_ms, int64_t *events, int64_t *launches);
 int slamgpu_timing_reset(slamgpu_t *h);
+/* Counters since creation: landmark rows re-columned by deferred resampling, resamples applied, ancestor-chain
+ * steps walked (see slam_b200/csrc/kernels.cuh, K7). */
+#define SLAMGPU_STAT_ROWS_MOVED 0
+#define SLAMGPU_STAT_RESAMPLES 1
+#define SLAMGPU_STAT_CHAIN_STEPS 2
+int64_t slamgpu_stat(slamgpu_t *h, int32_t which);
 /* Total kernel launches issued by this handle since creation. */
 int64_t slamgpu_launch_count(slamgpu_t *h);
 

@@ -13,7 +13,7 @@ EXPORTS = [
     "slamgpu_upload_particles", "slamgpu_upload_particles_tiled", "slamgpu_download_particles", "slamgpu_landmark_count", "slamgpu_predict",
     "slamgpu_update", "slamgpu_update_particles", "slamgpu_resample", "slamgpu_stage_noise",
     "slamgpu_compute_jacobians", "slamgpu_compute_jacobians_batch", "slamgpu_estimate", "slamgpu_download_decimated",
-    "slamgpu_timing_enable", "slamgpu_timing_read", "slamgpu_timing_reset", "slamgpu_launch_count",
+    "slamgpu_timing_enable", "slamgpu_timing_read", "slamgpu_timing_reset", "slamgpu_launch_count", "slamgpu_stat",
     "slamgpu_comm_unique_id", "slamgpu_comm_init",
 ]
 
@@ -22,7 +22,7 @@ class Config(C.Structure):
     _fields_ = [("n_particles", C.c_int64), ("nf_cap", C.c_int32), ("method", C.c_int32), ("wheel_base", C.c_float),
                 ("sigma_phi", C.c_float), ("n_effective", C.c_int32), ("use_heading", C.c_int32),
                 ("do_resample", C.c_int32), ("scan_mode", C.c_int32), ("device", C.c_int32), ("spare_rows", C.c_int32),
-                ("math_mode", C.c_int32), ("reserved", C.c_int32 * 3)]
+                ("math_mode", C.c_int32), ("log_epochs", C.c_int32), ("reserved", C.c_int32 * 2)]
 
 
 _lib = None
@@ -70,6 +70,8 @@ def load():
     L.slamgpu_timing_reset.argtypes = [vp]
     L.slamgpu_launch_count.argtypes = [vp]
     L.slamgpu_launch_count.restype = C.c_int64
+    L.slamgpu_stat.argtypes = [vp, C.c_int32]
+    L.slamgpu_stat.restype = C.c_int64
     L.slamgpu_comm_unique_id.argtypes = [vp]
     L.slamgpu_comm_init.argtypes = [vp, C.c_int32, C.c_int32, vp]
     _lib = L

@@ -40,7 +40,7 @@ class FastSLAM:
     """One FastSLAM1/FastSLAM2 particle set on one CUDA device."""
 
     def __init__(self, method, n_particles, nf_cap, wheel_base=4.0, sigma_phi=0.0, n_effective=None, use_heading=False,
-                 resample=True, scan_mode=SCAN_BLOCKED, device=0, spare_rows=0, math_mode=MATH_FAST):
+                 resample=True, scan_mode=SCAN_BLOCKED, device=0, spare_rows=0, math_mode=MATH_FAST, log_epochs=0):
         self._L = _lib.load()
         self._h = C.c_void_p()
         self.P = int(n_particles)
@@ -59,6 +59,7 @@ class FastSLAM:
         cfg.device = device
         cfg.spare_rows = spare_rows
         cfg.math_mode = math_mode
+        cfg.log_epochs = log_epochs
         self._check(self._L.slamgpu_create(C.byref(cfg), C.byref(self._h)))
 
     # -- plumbing ---------------------------------------------------------------
@@ -90,6 +91,11 @@ class FastSLAM:
     @property
     def launches(self):
         return self._L.slamgpu_launch_count(self._h)
+
+    def stats(self):
+        """rows re-columned by deferred resampling, resamples applied, ancestor-chain steps."""
+        return dict(rows_moved=self._L.slamgpu_stat(self._h, 0), resamples=self._L.slamgpu_stat(self._h, 1),
+                    chain_steps=self._L.slamgpu_stat(self._h, 2))
 
     def comm_init(self, rank, world, unique_id):
         buf = (C.c_char * 128).from_buffer_copy(bytes(unique_id))

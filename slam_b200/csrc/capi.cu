@@ -100,7 +100,7 @@ static void free_all(slamgpu *h) {
     for (auto e : h->free_events) cudaEventDestroy(e);
     void *dev[] = {h->pose[0], h->pose[1], h->w, h->lm_mean, h->lm_cov, h->gauss, h->unif_base, h->di_base, h->cdf,
                    h->mloc, h->sel, h->keep, h->tot_w, h->tot_c, h->tot_s, h->bmax, h->d_sc, h->d_z, h->d_row,
-                   h->d_rec_in, h->d_rec_out, h->d_est};
+                   h->d_rec_in, h->d_rec_out, h->d_est, h->keeplog, h->anc, h->d_phys};
     for (void *p : dev)
         if (p) cudaFree(p);
     if (h->h_sc) cudaFreeHost(h->h_sc);
@@ -128,6 +128,11 @@ static int setup_global(slamgpu *h) {
     CU(cudaMalloc(&h->tot_c, sizeof(float) * h->nbg));
     CU(cudaMalloc(&h->tot_s, sizeof(float) * h->nbg));
     CU(cudaMalloc(&h->bmax, sizeof(float) * h->nbg));
+    if (h->keeplog) {
+        cudaFree(h->keeplog);
+        h->keeplog = nullptr;
+    }
+    CU(cudaMalloc(&h->keeplog, sizeof(int) * (size_t) h->H * Pg));
     // stratifiedRandom's deterministic midpoints, by the reference's own fp32 accumulation run exactly N times
     // (core.cpp:751-759; oracle so_stratified_di).  Only this device's slots (+2 halo) are kept.
     std::vector<float> di(h->P + 2, 0.0f);
@@ -153,8 +158,10 @@ static int create_impl(const slamgpu_config *cfg, slamgpu *h) {
     h->stream = h->own_stream;
     for (int i = 0; i < 2; i++) CU(cudaMalloc(&h->pose[i], sizeof(float) * 12 * P));
     CU(cudaMalloc(&h->w, sizeof(float) * P));
-    CU(cudaMalloc(&h->lm_mean, sizeof(float2) * (size_t) h->ring_rows * P));
-    CU(cudaMalloc(&h->lm_cov, sizeof(float4) * (size_t) h->ring_rows * P));
+    CU(cudaMalloc(&h->lm_mean, sizeof(float2) * (size_t) h->rows_total * P));
+    CU(cudaMalloc(&h->lm_cov, sizeof(float4) * (size_t) h->rows_total * P));
+    CU(cudaMalloc(&h->anc, sizeof(int) * P));
+    CU(cudaMalloc(&h->d_phys, sizeof(int) * h->nf_cap));
     CU(cudaMalloc(&h->gauss, sizeof(float) * 3 * P));
     CU(cudaMalloc(&h->unif_base, sizeof(double) * (P + 2)));
     CU(cudaMalloc(&h->di_base, sizeof(float) * (P + 2)));
@@ -194,7 +201,12 @@ extern "C" int slamgpu_create(const slamgpu_config *cfg, slamgpu_t **out) {
     h->P = h->Pg = (size_t) cfg->n_particles;
     h->nf_cap = cfg->nf_cap;
     h->spare = cfg->spare_rows > 0 ? cfg->spare_rows : std::min(64, cfg->nf_cap);
-    h->ring_rows = h->nf_cap + h->spare;
+    h->rows_total = h->nf_cap + h->spare;
+    h->phys.resize(h->nf_cap);
+    for (int l = 0; l < h->nf_cap; l++) h->phys[l] = l;
+    for (int r = 0; r < h->spare; r++) h->free_rows.push_back(h->nf_cap + r);
+    h->row_epoch.assign(h->nf_cap, 0);
+    h->H = cfg->log_epochs > 0 ? std::max(4, cfg->log_epochs) : 64;
     int r = create_impl(cfg, h);
     if (r != SLAMGPU_OK) {
         std::string keep = g_err;
@@ -224,6 +236,102 @@ extern "C" int slamgpu_synchronize(slamgpu_t *h) {
 }
 extern "C" int slamgpu_landmark_count(slamgpu_t *h) { return h ? h->Nf : SLAMGPU_EINVAL; }
 extern "C" int64_t slamgpu_launch_count(slamgpu_t *h) { return h ? h->launches : 0; }
+extern "C" int64_t slamgpu_stat(slamgpu_t *h, int32_t which) {
+    if (!h) return 0;
+    switch (which) {
+        case SLAMGPU_STAT_ROWS_MOVED: return h->stat_rows_moved;
+        case SLAMGPU_STAT_RESAMPLES: return h->stat_resamples;
+        case SLAMGPU_STAT_CHAIN_STEPS: return h->stat_chain_steps;
+    }
+    return 0;
+}
+
+// ---- landmark row pool: deferred resampling of the maps (kernels.cuh K7) ---------------------------------------
+static int peer_maps(slamgpu *h, PeerMaps *pm) {
+    if (h->world > 1) return comm_peer_maps(h->comm, h, pm);
+    memset(pm, 0, sizeof(*pm));
+    pm->world = 1;
+    pm->pose[0][0] = h->pose[0];
+    pm->pose[1][0] = h->pose[1];
+    pm->mean[0] = h->lm_mean;
+    pm->cov[0] = h->lm_cov;
+    return SLAMGPU_OK;
+}
+
+// Brings the listed logical rows up to the current resample epoch: column p <- column anc(p) of the stored row.
+// Rows are grouped by the epoch they belong to (newest first, so that one ancestor chain is extended group by group)
+// and moved in chunks into free physical rows; the vacated rows return to the pool.
+static int materialise(slamgpu *h, const std::vector<int> &want) {
+    std::vector<std::pair<long long, int>> stale;
+    for (int l : want)
+        if (h->row_epoch[l] < h->epoch) stale.push_back({h->row_epoch[l], l});
+    if (stale.empty()) return SLAMGPU_OK;
+    std::sort(stale.begin(), stale.end(), [](const std::pair<long long, int> &a, const std::pair<long long, int> &b) {
+        return a.first != b.first ? a.first > b.first : a.second < b.second;
+    });
+    if (h->epoch - stale.back().first >= h->H)
+        return slam_fail(SLAMGPU_EINVAL, "internal: a landmark row fell out of the resample log");
+    PeerMaps pm;
+    RET(peer_maps(h, &pm));
+    const size_t P = h->P, Pg = h->Pg;
+    TimedSpan sp;
+    RET(span_begin(h, SLAMGPU_T_GATHER, &sp));
+    bool identity = true;      // h->anc not started yet
+    long long cur_e = h->epoch;  // epoch h->anc currently maps back to
+    size_t i = 0;
+    while (i < stale.size()) {
+        const long long e = stale[i].first;
+        size_t j = i;
+        while (j < stale.size() && stale[j].first == e) j++;
+        const int *anc_ptr;
+        if (identity && e == h->epoch - 1) {
+            anc_ptr = h->keeplog + (size_t) (h->epoch % h->H) * Pg + h->slot0;  // one epoch back: keep[] itself
+        } else {
+            k_chain<<<grid_for(P, 256), 256, 0, h->stream>>>(h->anc, P, (long long) h->slot0, (long long) Pg, h->keeplog,
+                                                            h->H, cur_e, e + 1, identity ? 1 : 0);
+            KCHECK();
+            LAUNCHED(h, SLAMGPU_T_GATHER);
+            h->stat_chain_steps += cur_e - e;
+            identity = false;
+            cur_e = e;
+            anc_ptr = h->anc;
+        }
+        size_t k = i;
+        while (k < j) {
+            const int n = (int) std::min<size_t>(std::min<size_t>(j - k, SLAM_MOVES_PER_LAUNCH), h->free_rows.size());
+            if (n <= 0) return slam_fail(SLAMGPU_EINVAL, "internal: no spare landmark rows");
+            RowMoves mv;
+            std::vector<int> vacated(n);
+            for (int q = 0; q < n; q++) {
+                const int l = stale[k + q].second;
+                mv.p[q].src = h->phys[l];
+                mv.p[q].dst = h->free_rows.back();
+                h->free_rows.pop_back();
+                vacated[q] = h->phys[l];
+                h->phys[l] = mv.p[q].dst;
+                h->row_epoch[l] = h->epoch;
+            }
+            // sharded: a destination row was a source of an earlier chunk; no rank may overwrite it while a peer reads
+            if (h->world > 1) RET(comm_barrier(h->comm, h->stream));
+            dim3 grid(grid_for(P, 256), (n + SLAM_GATHER_ROWS - 1) / SLAM_GATHER_ROWS);
+            k_materialise_rows<<<grid, 256, 0, h->stream>>>(pm, h->ring(), P, anc_ptr, (long long) Pg, mv, n);
+            KCHECK();
+            LAUNCHED(h, SLAMGPU_T_GATHER);
+            h->stat_rows_moved += n;
+            for (int q = 0; q < n; q++) h->free_rows.insert(h->free_rows.begin(), vacated[q]);
+            k += n;
+        }
+        i = j;
+    }
+    RET(span_end(h, &sp));
+    return SLAMGPU_OK;
+}
+
+static int materialise_all(slamgpu *h) {
+    std::vector<int> all(h->Nf);
+    for (int l = 0; l < h->Nf; l++) all[l] = l;
+    return materialise(h, all);
+}
 
 // ---- state transfer ---------------------------------------------------------------------------------------
 extern "C" int slamgpu_upload_particles(slamgpu_t *h, const float *xv, const float *Pv, const float *w,
@@ -237,8 +345,10 @@ extern "C" int slamgpu_upload_particles(slamgpu_t *h, const float *xv, const flo
     if (xv) CU(cudaMemcpyAsync(s.xv, xv, sizeof(float) * 3 * P, cudaMemcpyHostToDevice, h->stream));
     if (Pv) CU(cudaMemcpyAsync(s.Pv, Pv, sizeof(float) * 9 * P, cudaMemcpyHostToDevice, h->stream));
     if (w) CU(cudaMemcpyAsync(s.w, w, sizeof(float) * P, cudaMemcpyHostToDevice, h->stream));
+    if ((lm_mean != nullptr) != (lm_cov != nullptr)) RET(materialise_all(h));  // half a row keeps its other half
     for (int l = 0; l < Nf; l++) {
         const size_t row = (size_t) h->phys_row(l);
+        if (lm_mean && lm_cov) h->row_epoch[l] = h->epoch;
         if (lm_mean)
             CU(cudaMemcpyAsync(h->lm_mean + row * P, lm_mean + (size_t) l * P * 2, sizeof(float2) * P,
                                cudaMemcpyHostToDevice, h->stream));
@@ -279,7 +389,10 @@ extern "C" int slamgpu_upload_particles_tiled(slamgpu_t *h, int64_t Pt, const fl
             if (e == cudaSuccess)
                 e = cudaMemcpyAsync(tc, lm_cov + (size_t) l0 * T * 4, sizeof(float4) * n * T, cudaMemcpyHostToDevice, h->stream);
             if (e != cudaSuccess) { rc = SLAMGPU_ECUDA; break; }
-            k_tile_rows<<<dim3(grid_for(P, 256), n), 256, 0, h->stream>>>(tm, tc, T, h->ring(), P, l0);
+            e = cudaMemcpyAsync(h->d_phys, h->phys.data() + l0, sizeof(int) * n, cudaMemcpyHostToDevice, h->stream);
+            if (e != cudaSuccess) { rc = SLAMGPU_ECUDA; break; }
+            k_tile_rows<<<dim3(grid_for(P, 256), n), 256, 0, h->stream>>>(tm, tc, T, h->ring(), P, h->d_phys);
+            for (int l = l0; l < l0 + n; l++) h->row_epoch[l] = h->epoch;
             h->launches++;
             if (cudaStreamSynchronize(h->stream) != cudaSuccess) { rc = SLAMGPU_ECUDA; break; }
         }
@@ -295,6 +408,7 @@ extern "C" int slamgpu_download_particles(slamgpu_t *h, float *xv, float *Pv, fl
     if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
     CU(cudaSetDevice(h->cfg.device));
     const size_t P = h->P;
+    if (lm_mean || lm_cov) RET(materialise_all(h));
     PoseSoA s = h->soa(h->cur);
     if (xv) CU(cudaMemcpyAsync(xv, s.xv, sizeof(float) * 3 * P, cudaMemcpyDeviceToHost, h->stream));
     if (Pv) CU(cudaMemcpyAsync(Pv, s.Pv, sizeof(float) * 9 * P, cudaMemcpyDeviceToHost, h->stream));
@@ -416,6 +530,7 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
     const float4 Rm = make_float4(R[0], R[1], R[2], R[3]);
     const size_t P = h->P;
     if (K > 0) {
+        RET(materialise(h, std::vector<int>(idf, idf + K)));  // observed rows catch up with the resamples since
         for (int i = 0; i < K; i++) rows[i] = h->phys_row(idf[i]);
         RET(stage_obs_host(h, zf, rows.data(), K));
         ObsSet o;
@@ -439,7 +554,10 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
         RET(span_end(h, &sp));
     }
     if (Kn > 0) {
-        for (int i = 0; i < Kn; i++) rows[i] = h->phys_row(h->Nf + i);
+        for (int i = 0; i < Kn; i++) {
+            rows[i] = h->phys_row(h->Nf + i);
+            h->row_epoch[h->Nf + i] = h->epoch;
+        }
         RET(stage_obs_host(h, zn, rows.data(), Kn));
         ObsSet o;
         o.z = h->d_z;
@@ -545,26 +663,35 @@ static int resample_indices(slamgpu *h) {
     return SLAMGPU_OK;
 }
 
-static int gather_local(slamgpu *h) {
-    const size_t P = h->P;
-    const float new_w = 1.0f / (float) h->Pg;
-    PoseSoA src = h->soa(h->cur), dst = h->soa(h->cur ^ 1);
-    k_gather_pose<<<grid_for(P, 256), 256, 0, h->stream>>>(src.xv, src.Pv, dst.xv, dst.Pv, h->w, h->keep, P,
-                                                           (long long) h->slot0, (long long) h->Pg, new_w);
+// The "particles[i] = oldParticles[keep[i]]" of core.cpp:739-748: poses now, maps deferred (kernels.cuh K7).
+static int resample_state(slamgpu *h) {
+    const size_t P = h->P, Pg = h->Pg;
+    const float new_w = 1.0f / (float) Pg;
+    h->epoch++;
+    h->stat_resamples++;
+    int *slot = h->keeplog + (size_t) (h->epoch % h->H) * Pg;
+    CU(cudaMemcpyAsync(slot + h->slot0, h->keep, sizeof(int) * P, cudaMemcpyDeviceToDevice, h->stream));
+    if (h->world > 1) RET(comm_allgather_i32(h->comm, slot, P, h->stream));
+    PeerMaps pm;
+    RET(peer_maps(h, &pm));
+    // sharded: every rank's update kernels must be done before a peer reads its poses, and the buffer written here
+    // was the source of the previous resample
+    if (h->world > 1) RET(comm_barrier(h->comm, h->stream));
+    k_gather_pose<<<grid_for(P, 256), 256, 0, h->stream>>>(pm, h->cur, h->pose[h->cur ^ 1], h->w, h->keep, P,
+                                                           (long long) Pg, new_w);
     KCHECK();
     LAUNCHED(h, SLAMGPU_T_GATHER);
     h->cur ^= 1;
-    const int S = h->spare;
-    for (int l0 = 0; l0 < h->Nf; l0 += S) {
-        const int nrows = std::min(S, h->Nf - l0);
-        dim3 grid(grid_for(P, 256), (nrows + SLAM_GATHER_ROWS - 1) / SLAM_GATHER_ROWS);
-        k_gather_rows<<<grid, 256, 0, h->stream>>>(h->ring(), P, h->keep, l0, nrows, S, (long long) h->slot0,
-                                                   (long long) h->Pg);
-        KCHECK();
-        LAUNCHED(h, SLAMGPU_T_GATHER);
-    }
-    h->ring_base = (h->ring_base - S + h->ring_rows) % h->ring_rows;
-    return SLAMGPU_OK;
+    // background trickle: the stalest rows, enough per resample that no row's backlog reaches the log length
+    const int per = (h->Nf + (h->H - 3)) / (h->H - 2);
+    std::vector<std::pair<long long, int>> order;
+    for (int l = 0; l < h->Nf; l++)
+        if (h->row_epoch[l] < h->epoch) order.push_back({h->row_epoch[l], l});
+    std::sort(order.begin(), order.end());
+    std::vector<int> pick;
+    for (size_t i = 0; i < order.size(); i++)
+        if ((int) i < per || h->epoch - order[i].first >= h->H - 1) pick.push_back(order[i].second);
+    return materialise(h, pick);
 }
 
 extern "C" int slamgpu_resample(slamgpu_t *h, const double *unif, int32_t *keep_out, float *neff,
@@ -598,10 +725,7 @@ extern "C" int slamgpu_resample(slamgpu_t *h, const double *unif, int32_t *keep_
     if (did) {
         TimedSpan sg;
         RET(span_begin(h, SLAMGPU_T_GATHER, &sg));
-        if (h->world > 1)
-            RET(comm_gather_sharded(h->comm, h));
-        else
-            RET(gather_local(h));
+        RET(resample_state(h));
         RET(span_end(h, &sg));
     }
     if (neff) *neff = ne;
@@ -669,8 +793,9 @@ extern "C" int slamgpu_compute_jacobians_batch(slamgpu_t *h, const int32_t *idf,
     std::vector<float> z(2 * (size_t) K, 0.0f);
     for (int i = 0; i < K; i++) {
         if (idf[i] < 0 || idf[i] >= h->Nf) return slam_fail(SLAMGPU_EINVAL, "idf entry outside [0, Nf)");
-        rows[i] = h->phys_row(idf[i]);
     }
+    RET(materialise(h, std::vector<int>(idf, idf + K)));
+    for (int i = 0; i < K; i++) rows[i] = h->phys_row(idf[i]);
     RET(stage_obs_host(h, z.data(), rows.data(), K));
     float4 *dout = nullptr;
     const size_t bytes = sizeof(float) * 16 * (size_t) K * h->P;
@@ -728,8 +853,12 @@ extern "C" int slamgpu_download_decimated(slamgpu_t *h, int64_t stride, float *x
             return slam_fail(SLAMGPU_ENOMEM, "decimated landmark buffer");
         }
     }
-    k_decimate<<<grid_for(n, 256), 256, 0, h->stream>>>(h->soa(h->cur), h->ring(), h->P, (size_t) stride, n, h->Nf, dx,
-                                                        dl);
+    if (dl) {
+        RET(materialise_all(h));
+        CU(cudaMemcpyAsync(h->d_phys, h->phys.data(), sizeof(int) * h->Nf, cudaMemcpyHostToDevice, h->stream));
+    }
+    k_decimate<<<grid_for(n, 256), 256, 0, h->stream>>>(h->soa(h->cur), h->ring(), h->P, (size_t) stride, n, h->Nf,
+                                                        h->d_phys, dx, dl);
     h->launches++;
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaMemcpyAsync(xv_out, dx, sizeof(float) * 3 * n, cudaMemcpyDeviceToHost, h->stream);

@@ -4,9 +4,8 @@
 //     through NCCL, loaded at run time from libnccl.so.2 (the copy torch already mapped when the caller is a
 //     torchrun rank, else the system one) so that a single-device build has no NCCL dependency;
 //   * particle migration is NOT a collective: every rank maps its peers' pose and landmark buffers (CUDA IPC over
-//     NVLink / NVSwitch) and the gather kernels read particles[keep[i]] straight from the owning device, row batch by
-//     row batch, with a stream-ordered barrier between batches because the ring (kernels.cuh) recycles the rows the
-//     previous batch was read from.
+//     NVLink / NVSwitch) and the gather kernels (kernels.cuh K7) read particles[keep[i]] straight from the owning
+//     device, with a stream-ordered barrier between batches because freed physical rows are recycled.
 #include <dlfcn.h>
 #include <nccl.h>
 
@@ -16,7 +15,6 @@
 
 using namespace slam;
 
-#define SLAM_MAX_RANKS 8
 
 struct NcclApi {
     void *lib = nullptr;
@@ -52,12 +50,6 @@ static int load_nccl(NcclApi *api, std::string *err) {
 }
 
 static NcclApi g_nccl;
-
-struct PeerMaps {
-    const float *pose[2][SLAM_MAX_RANKS];
-    const float2 *mean[SLAM_MAX_RANKS];
-    const float4 *cov[SLAM_MAX_RANKS];
-};
 
 struct SlamComm {
     int rank = 0, world = 1, device = 0;
@@ -177,86 +169,21 @@ static int open_peers(SlamComm *c, slamgpu *h) {
         c->peers.mean[r] = (const float2 *) p[2];
         c->peers.cov[r] = (const float4 *) p[3];
     }
+    c->peers.world = c->world;
     c->peers_open = true;
     return SLAMGPU_OK;
 }
 
-// ---- gather kernels with sources on any rank -------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_gather_pose_sharded(PeerMaps pm, int cur, float *__restrict__ dst_pose,
-                                                             float *__restrict__ w, const int *__restrict__ keep,
-                                                             size_t P, long long n_global, float new_w) {
-    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= P) return;
-    long long k = keep[p];
-    if (k < 0) k = n_global - 1;
-    const int r = (int) (k / (long long) P);
-    const size_t sidx = (size_t) (k - (long long) r * (long long) P);
-    const float *src = pm.pose[cur][r];
-#pragma unroll
-    for (int c = 0; c < 12; c++) dst_pose[c * P + p] = src[c * P + sidx];
-    w[p] = new_w;
-}
-
-__global__ void __launch_bounds__(256) k_gather_rows_sharded(PeerMaps pm, MapRing m, size_t P,
-                                                             const int *__restrict__ keep, int l0, int nrows, int shift,
-                                                             long long n_global) {
-    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= P) return;
-    long long k = keep[p];
-    if (k < 0) k = n_global - 1;
-    const int r = (int) (k / (long long) P);
-    const size_t sidx = (size_t) (k - (long long) r * (long long) P);
-    const float2 *smean = pm.mean[r];
-    const float4 *scov = pm.cov[r];
-    const int lbeg = l0 + blockIdx.y * SLAM_GATHER_ROWS;
-    float2 a[SLAM_GATHER_ROWS];
-    float4 c[SLAM_GATHER_ROWS];
-#pragma unroll
-    for (int q = 0; q < SLAM_GATHER_ROWS; q++) {
-        const int l = lbeg + q;
-        if (l < l0 + nrows) {
-            const int srow = (m.ring_base + l) % m.ring_rows;  // every rank's ring moves in lockstep
-            a[q] = smean[(size_t) srow * P + sidx];
-            c[q] = scov[(size_t) srow * P + sidx];
-        }
-    }
-#pragma unroll
-    for (int q = 0; q < SLAM_GATHER_ROWS; q++) {
-        const int l = lbeg + q;
-        if (l < l0 + nrows) {
-            const int drow = (m.ring_base + l - shift + m.ring_rows) % m.ring_rows;
-            __stcs(&m.mean[(size_t) drow * P + p], a[q]);
-            __stcs(&m.cov[(size_t) drow * P + p], c[q]);
-        }
-    }
-}
-
-int comm_gather_sharded(SlamComm *c, slamgpu *h) {
+int comm_peer_maps(SlamComm *c, slamgpu *h, PeerMaps *out) {
     RET(open_peers(c, h));
-    const size_t P = h->P;
-    const float new_w = 1.0f / (float) h->Pg;
-    const unsigned gx = (unsigned) ((P + 255) / 256);
-    // everyone's update kernels must have finished before any rank reads a peer's state
-    RET(barrier(c, h->stream));
-    k_gather_pose_sharded<<<gx, 256, 0, h->stream>>>(c->peers, h->cur, h->pose[h->cur ^ 1], h->w, h->keep, P,
-                                                     (long long) h->Pg, new_w);
-    CU(cudaGetLastError());
-    h->launches++;
-    h->t_launches[SLAMGPU_T_GATHER]++;
-    const int S = h->spare;
-    for (int l0 = 0; l0 < h->Nf; l0 += S) {
-        const int nrows = (h->Nf - l0 < S) ? h->Nf - l0 : S;
-        dim3 grid(gx, (nrows + SLAM_GATHER_ROWS - 1) / SLAM_GATHER_ROWS);
-        k_gather_rows_sharded<<<grid, 256, 0, h->stream>>>(c->peers, h->ring(), P, h->keep, l0, nrows, S,
-                                                           (long long) h->Pg);
-        CU(cudaGetLastError());
-        h->launches++;
-        h->t_launches[SLAMGPU_T_GATHER]++;
-        RET(barrier(c, h->stream));  // nobody may recycle these source rows before every rank has read them
-    }
-    if (h->Nf == 0) RET(barrier(c, h->stream));
-    h->cur ^= 1;
-    h->ring_base = (h->ring_base - S + h->ring_rows) % h->ring_rows;
+    *out = c->peers;
+    return SLAMGPU_OK;
+}
+
+int comm_barrier(SlamComm *c, cudaStream_t st) { return barrier(c, st); }
+
+int comm_allgather_i32(SlamComm *c, int *buf, size_t count, cudaStream_t st) {
+    NC(g_nccl.AllGather(buf + (size_t) c->rank * count, buf, count, ncclInt32, c->comm, st));
     return SLAMGPU_OK;
 }
 

@@ -28,6 +28,7 @@ int slam_fail(int code, const std::string &msg);  // records the text for slamgp
 struct SlamComm;
 using slam::EstPartial;
 using slam::MapRing;
+using slam::PeerMaps;
 using slam::PoseSoA;
 
 struct Scalars {  // device + pinned mirror
@@ -47,7 +48,18 @@ struct slamgpu {
     size_t Pg = 0;        // global particles (== P unless sharded)
     size_t slot0 = 0;     // first global particle held here
     int rank = 0, world = 1;
-    int nf_cap = 0, Nf = 0, spare = 0, ring_rows = 0, ring_base = 0;
+    int nf_cap = 0, Nf = 0, spare = 0, rows_total = 0;
+    // landmark row pool (see kernels.cuh K7): logical -> physical table, free physical rows, and the resample epoch
+    // each logical row's columns belong to
+    std::vector<int> phys, free_rows;
+    std::vector<long long> row_epoch;
+    long long epoch = 0;         // number of resamples applied to the poses so far
+    int H = 0;                   // epochs of keep[] kept in the log
+    int *keeplog = nullptr;      // [H][Pg] global keep arrays, epoch e at slot e % H
+    int *anc = nullptr;          // [P] scratch: composed ancestor map
+    slam::RowPair *d_pairs = nullptr, *h_pairs = nullptr;  // row-move lists (device / pinned), nf_cap entries
+    int *d_phys = nullptr;       // device copy of phys[] for the download helpers
+    int64_t stat_rows_moved = 0, stat_resamples = 0, stat_chain_steps = 0;
     cudaStream_t stream = nullptr, own_stream = nullptr;
     float *pose[2] = {nullptr, nullptr};  // each: xv[3][P] then Pv[9][P]
     int cur = 0;
@@ -94,11 +106,10 @@ struct slamgpu {
         MapRing m;
         m.mean = lm_mean;
         m.cov = lm_cov;
-        m.ring_rows = ring_rows;
-        m.ring_base = ring_base;
+        m.rows = rows_total;
         return m;
     }
-    int phys_row(int l) const { return (ring_base + l) % ring_rows; }
+    int phys_row(int l) const { return phys[l]; }
     double *unif() const { return unif_base + 2; }
     float *di() const { return di_base + 2; }
 };
@@ -112,6 +123,9 @@ void comm_destroy(SlamComm *c);
 int comm_allgather_f32(SlamComm *c, float *buf, size_t count, cudaStream_t st);
 // unif_base[0..1] <- the previous rank's last two uniforms (the search kernel's 2-slot halo).
 int comm_halo_unif(SlamComm *c, double *unif_base, size_t P, cudaStream_t st);
-// particles[i] = old[keep[i]] with sources on any rank (peer-mapped reads inside the gather kernels).
-int comm_gather_sharded(SlamComm *c, slamgpu *h);
+// Maps every peer's pose / landmark buffers (CUDA IPC, once) and returns the table the gather kernels index by rank.
+int comm_peer_maps(SlamComm *c, slamgpu *h, PeerMaps *out);
+// Stream-ordered barrier over all ranks (nobody passes until every rank's stream has reached it).
+int comm_barrier(SlamComm *c, cudaStream_t st);
+int comm_allgather_i32(SlamComm *c, int *buf, size_t count, cudaStream_t st);
 int comm_reduce_estimate(SlamComm *c, slamgpu *h, double *sx, double *sy, float wmax, long long imax, double *theta);

@@ -2,8 +2,9 @@
 //
 // One thread owns one particle; state is structure-of-arrays so that every warp access is one contiguous
 // segment (pose planes: 128 B; landmark rows: float2 -> 256 B, float4 -> 512 B per warp).  Landmark rows live in a
-// ring of (nf_cap + spare) physical rows: logical row l is physical row (ring_base + l) % ring_rows, which lets the
-// resample gather move the whole map without a second full-size buffer (gather_rows below).
+// pool of (nf_cap + spare) physical rows behind a host-side logical -> physical table; resampling does NOT copy the
+// map: it appends keep[] to a log, and a row is brought up to date (k_chain + k_materialise_rows below) only when
+// it is next touched, or when its backlog would outgrow the log.
 //
 // All contractions are 2x2 / 3x3 per particle: CUDA-core fp32, no tensor cores (nothing here is GEMM shaped).
 #pragma once
@@ -704,55 +705,82 @@ __global__ void k_neff(const float *__restrict__ s2, float *__restrict__ neff_ou
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// K7  resample gather: particles[i] = old[keep[i]], w = 1/N (core.cpp:736-748).  keep < 0 (undefined behaviour in
-// the reference) clamps to the last particle.  Local variant: every source index lies on this device
-// (src_offset = first global index held here).
+// K7  resampling the state: particles[i] = old[keep[i]], w = 1/N (core.cpp:736-748).  keep < 0 (undefined behaviour in
+// the reference) clamps to the last particle.
+//
+// Poses (48 B per particle) are gathered eagerly into the second pose buffer.  The landmark maps (24 B x Nf per
+// particle: 25 GB at 2^20 x 1024) are NOT: the reference copies all of them on every resample although one update
+// touches only the K observed rows.  Here every resample appends its keep[] to a log of the last H epochs, every row
+// remembers the epoch its columns belong to, and a row is re-columned when it is next needed:
+//     column p of the up-to-date row = column anc(p) of the stored row,
+//     anc = keep_{e+1} o keep_{e+2} o ... o keep_E   (k_chain walks the log; a composition of monotone maps)
+// The result is the reference's, bit for bit (a copy commutes with being postponed); the traffic per resample drops
+// from 2*Nf rows to the rows actually read plus a trickle of background rows that bounds the log.
+// Sources may live on a peer device when particles are sharded (PeerMaps; rank = global index / P).
 // ---------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_gather_pose(const float *__restrict__ src_xv, const float *__restrict__ src_Pv,
-                                                     float *__restrict__ dst_xv, float *__restrict__ dst_Pv,
+__global__ void __launch_bounds__(256) k_gather_pose(PeerMaps pm, int cur, float *__restrict__ dst_pose,
                                                      float *__restrict__ w, const int *__restrict__ keep, size_t P,
-                                                     long long src_offset, long long n_global, float new_w) {
+                                                     long long n_global, float new_w) {
     const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= P) return;
     long long k = keep[p];
     if (k < 0) k = n_global - 1;
-    const size_t sidx = (size_t) (k - src_offset);
+    const int r = (pm.world > 1) ? (int) (k / (long long) P) : 0;
+    const size_t sidx = (size_t) (k - (long long) r * (long long) P);
+    const float *src = pm.pose[cur][r];
 #pragma unroll
-    for (int c = 0; c < 3; c++) dst_xv[c * P + p] = src_xv[c * P + sidx];
-#pragma unroll
-    for (int c = 0; c < 9; c++) dst_Pv[c * P + p] = src_Pv[c * P + sidx];
+    for (int c = 0; c < 12; c++) dst_pose[c * P + p] = src[c * P + sidx];
     w[p] = new_w;
 }
 
-// Rows [l0, l0 + nrows) of the map, logical -> shifted ring position.  grid = (ceil(P/256), row groups); each thread
-// keeps its source index in a register and moves ROWS_PER_THREAD rows (independent loads in flight).  keep is
-// non-decreasing, so reads are monotone with duplicates served by L1/L2, writes are fully coalesced.
-__global__ void __launch_bounds__(256) k_gather_rows(MapRing m, size_t P, const int *__restrict__ keep, int l0,
-                                                     int nrows, int shift, long long src_offset, long long n_global) {
+// anc[p] <- keep_{e_to}[ ... keep_{e_from}[ start ] ... ] for e = e_from down to e_to, where start = anc[p] (continuing
+// a chain) or this device's global slot (start_identity).  keeplog holds the last H global keep arrays, epoch e at
+// slot e % H, each n_global ints.
+__global__ void __launch_bounds__(256) k_chain(int *__restrict__ anc, size_t P, long long slot0, long long n_global,
+                                               const int *__restrict__ keeplog, int H, long long e_from,
+                                               long long e_to, int start_identity) {
     const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= P) return;
-    long long k = keep[p];
+    long long a = start_identity ? slot0 + (long long) p : (long long) anc[p];
+    for (long long e = e_from; e >= e_to; e--) {
+        long long k = keeplog[(size_t) (e % H) * (size_t) n_global + (size_t) a];
+        a = (k < 0) ? n_global - 1 : k;
+    }
+    anc[p] = (int) a;
+}
+
+// dst row [p] = src row [anc[p]] for a list of row moves; grid = (ceil(P/256), ceil(nrows/SLAM_GATHER_ROWS)).  Each
+// thread keeps its source column in a register and moves SLAM_GATHER_ROWS rows (independent loads in flight).  anc
+// is non-decreasing, so reads are monotone with duplicates served by L1/L2; writes are fully coalesced.
+__global__ void __launch_bounds__(256) k_materialise_rows(PeerMaps pm, MapRing m, size_t P,
+                                                          const int *__restrict__ anc, long long n_global,
+                                                          const RowMoves mv, int nrows) {
+    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    long long k = anc[p];
     if (k < 0) k = n_global - 1;
-    const size_t sidx = (size_t) (k - src_offset);
-    const int lbeg = l0 + blockIdx.y * SLAM_GATHER_ROWS;
+    const int r = (pm.world > 1) ? (int) (k / (long long) P) : 0;
+    const size_t sidx = (size_t) (k - (long long) r * (long long) P);
+    const float2 *smean = pm.mean[r];
+    const float4 *scov = pm.cov[r];
+    const int i0 = blockIdx.y * SLAM_GATHER_ROWS;
     float2 a[SLAM_GATHER_ROWS];
     float4 c[SLAM_GATHER_ROWS];
+    int dst[SLAM_GATHER_ROWS];
 #pragma unroll
-    for (int r = 0; r < SLAM_GATHER_ROWS; r++) {
-        const int l = lbeg + r;
-        if (l < l0 + nrows) {
-            const int srow = (m.ring_base + l) % m.ring_rows;
-            a[r] = m.mean[(size_t) srow * P + sidx];
-            c[r] = m.cov[(size_t) srow * P + sidx];
+    for (int q = 0; q < SLAM_GATHER_ROWS; q++) {
+        if (i0 + q < nrows) {
+            const RowPair rp = mv.p[i0 + q];
+            dst[q] = rp.dst;
+            a[q] = smean[(size_t) rp.src * P + sidx];
+            c[q] = scov[(size_t) rp.src * P + sidx];
         }
     }
 #pragma unroll
-    for (int r = 0; r < SLAM_GATHER_ROWS; r++) {
-        const int l = lbeg + r;
-        if (l < l0 + nrows) {
-            const int drow = (m.ring_base + l - shift + m.ring_rows) % m.ring_rows;
-            __stcs(&m.mean[(size_t) drow * P + p], a[r]);
-            __stcs(&m.cov[(size_t) drow * P + p], c[r]);
+    for (int q = 0; q < SLAM_GATHER_ROWS; q++) {
+        if (i0 + q < nrows) {
+            __stcs(&m.mean[(size_t) dst[q] * P + p], a[q]);
+            __stcs(&m.cov[(size_t) dst[q] * P + p], c[q]);
         }
     }
 }
@@ -831,15 +859,15 @@ __global__ void __launch_bounds__(256) k_estimate_final(const EstPartial *__rest
 
 // Strided download helper: every stride-th particle's pose and landmark means, packed.
 __global__ void __launch_bounds__(256) k_decimate(PoseSoA s, MapRing m, size_t P, size_t stride, size_t n, int Nf,
-                                                  float *__restrict__ xv_out, float2 *__restrict__ lm_out) {
+                                                  const int *__restrict__ phys, float *__restrict__ xv_out,
+                                                  float2 *__restrict__ lm_out) {
     const size_t q = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= n) return;
     const size_t p = q * stride;
     for (int c = 0; c < 3; c++) xv_out[c * n + q] = s.xv[c * P + p];
     if (lm_out)
         for (int l = 0; l < Nf; l++) {
-            const int row = (m.ring_base + l) % m.ring_rows;
-            lm_out[(size_t) l * n + q] = m.mean[(size_t) row * P + p];
+            lm_out[(size_t) l * n + q] = m.mean[(size_t) phys[l] * P + p];
         }
 }
 
@@ -851,11 +879,11 @@ __global__ void __launch_bounds__(256) k_tile_planes(const float *__restrict__ t
     for (int c = 0; c < planes; c++) dst[c * P + p] = tile[c * Pt + p % Pt];
 }
 __global__ void __launch_bounds__(256) k_tile_rows(const float2 *__restrict__ tmean, const float4 *__restrict__ tcov,
-                                                   size_t Pt, MapRing m, size_t P, int l0) {
+                                                   size_t Pt, MapRing m, size_t P, const int *__restrict__ phys) {
     const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= P) return;
     const int l = blockIdx.y;  // row inside the uploaded chunk
-    const int row = (m.ring_base + l0 + l) % m.ring_rows;
+    const int row = phys[l];  // physical row of the l-th row of this chunk
     m.mean[(size_t) row * P + p] = tmean[(size_t) l * Pt + p % Pt];
     m.cov[(size_t) row * P + p] = tcov[(size_t) l * Pt + p % Pt];
 }

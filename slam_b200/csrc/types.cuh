@@ -14,11 +14,26 @@ struct PoseSoA {  // xv[3][P], Pv[9][P], w[P]
     float *w;
 };
 
-struct MapRing {  // landmark rows
-    float2 *mean;  // [ring_rows][P]
-    float4 *cov;   // [ring_rows][P], column-major linear 2x2 (core.cpp:613-615)
-    int ring_rows;
-    int ring_base;
+struct MapRing {   // landmark rows: a pool of (nf_cap + spare) physical rows; the host keeps the logical -> physical table
+    float2 *mean;  // [rows][P]
+    float4 *cov;   // [rows][P], column-major linear 2x2 (core.cpp:613-615)
+    int rows;
+};
+
+#define SLAM_MAX_RANKS 8
+struct PeerMaps {  // this device's and (when sharded) the peers' buffers, indexed by rank
+    const float *pose[2][SLAM_MAX_RANKS];
+    const float2 *mean[SLAM_MAX_RANKS];
+    const float4 *cov[SLAM_MAX_RANKS];
+    int world;
+};
+
+struct RowPair {  // one row move of a materialisation: physical source row -> physical destination row
+    int src, dst;
+};
+#define SLAM_MOVES_PER_LAUNCH 64
+struct RowMoves {  // passed to the kernel by value (512 B): no staging buffer to keep alive
+    RowPair p[SLAM_MOVES_PER_LAUNCH];
 };
 
 struct EstPartial {

@@ -201,9 +201,13 @@ def test_synthetic_k32_update_and_estimate(sb, oracle):
     assert np.array_equal(xv_d, g["xv"][:, ::7]) and np.array_equal(lm_d, g["lm_mean"][:, ::7])
 
 
-def test_resample_gather_moves_whole_map(sb, oracle):
-    """Forced resample: poses and every landmark row follow keep[] exactly (a copy: bit-exact), across more rows
-    than the ring's spare rows so that several batches run, and twice so that the ring wraps."""
+@pytest.mark.parametrize("log_epochs,spare", [(4, 5), (64, 64)])
+def test_resample_moves_whole_map_deferred(sb, oracle, log_epochs, spare):
+    """Forced resamples: poses and EVERY landmark row must follow keep[] exactly (a copy: bit-exact) although the
+    library defers the map gather (kernels.cuh K7).  Rows are touched at different times (a subset is read through
+    compute_jacobians_batch between resamples, the whole set only every third round), the keep[] log is as short as
+    4 epochs so that the background trickle and the mandatory catch-up both run, and there are fewer spare rows than
+    rows to move so that the row pool recycles."""
     from gpu_util import gpu_snapshot, make_backend, upload_state
     from oracle.pyoracle import State
     P, Nf = 3000, 23
@@ -211,21 +215,33 @@ def test_resample_gather_moves_whole_map(sb, oracle):
     s = State(P, Nf + 2)
     s.xv[:] = rng.standard_normal((3, P))
     s.Pv[:] = rng.standard_normal((9, P))
-    s.lm_mean[:Nf] = rng.standard_normal((Nf, P, 2))
+    s.lm_mean[:Nf] = rng.standard_normal((Nf, P, 2)) + 50  # away from the pose so that the jacobian read is finite
     s.lm_cov[:Nf] = rng.standard_normal((Nf, P, 4))
     s.Nf = Nf
-    f = make_backend(2, P, Nf + 2, n_effective=P + 1, scan_mode=sb.SCAN_BLOCKED, spare_rows=5)
-    for rnd in range(3):
+    import slam_b200
+    from scenario import SIGMA_PHI, WHEELBASE
+    f = slam_b200.FastSLAM(2, P, Nf + 2, wheel_base=WHEELBASE, sigma_phi=SIGMA_PHI, n_effective=P + 1,
+                           scan_mode=sb.SCAN_BLOCKED, spare_rows=spare, log_epochs=log_epochs)
+    upload_state(f, s)
+    for rnd in range(13):
         s.w[:] = rng.random(P).astype(np.float32) ** 4
-        upload_state(f, s) if rnd == 0 else f.upload(w=s.w)
+        f.upload(w=s.w)
         unif = rng.random(P)
         keep, neff, did = f.resample(unif, want_keep=True)
         keep_o, neff_o, did_o = oracle.resample(s, unif, P + 1, True, scan_mode=1)
         assert did and did_o and np.array_equal(keep, keep_o) and neff == neff_o
-        g = gpu_snapshot(f)
-        for k in ("xv", "Pv", "w"):
-            assert np.array_equal(g[k], getattr(s, k)), (rnd, k)
-        assert np.array_equal(g["lm_mean"], s.lm_mean[:Nf]) and np.array_equal(g["lm_cov"], s.lm_cov[:Nf])
+        if rnd % 2 == 0:  # touch a few rows only
+            f.compute_jacobians_batch(rng.choice(Nf, size=4, replace=False).astype(np.int32), R_DEFAULT)
+        if rnd % 3 == 2 or rnd == 12:
+            g = gpu_snapshot(f)
+            for k in ("xv", "Pv", "w"):
+                assert np.array_equal(g[k], getattr(s, k)), (rnd, k)
+            assert np.array_equal(g["lm_mean"], s.lm_mean[:Nf]), rnd
+            assert np.array_equal(g["lm_cov"], s.lm_cov[:Nf]), rnd
+    st = f.stats()
+    assert st["resamples"] == 13 and st["rows_moved"] > 0
+    if log_epochs == 64:  # deferred: far fewer row moves than the reference's Nf per resample
+        assert st["rows_moved"] < 13 * Nf
 
 
 def test_error_paths(sb):
