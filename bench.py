@@ -308,6 +308,7 @@ def run_ours(a):
     f.timing_reset()
     state.update(resamples=0, steps=0)
     launches0 = f.launches
+    stats0 = f.stats()
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
@@ -322,6 +323,9 @@ def run_ours(a):
     dev_ms = max_over_ranks(e0.elapsed_time(e1))
     clk = clocks.stop() if rank == 0 else None
     launches = f.launches - launches0
+    stats1 = f.stats()
+    rows_moved = stats1["rows_moved"] - stats0["rows_moved"]
+    n_resamples = stats1["resamples"] - stats0["resamples"]
     fam = f.timing_read()
     f.timing_enable(False)
     resample_rate = state["resamples"] / max(1, state["steps"])
@@ -344,19 +348,23 @@ def run_ours(a):
 
     # ---- roofline of the dominant kernel family (device time from CUDA events inside the timed region) --------
     peak, peak_src = peaks()
-    alg = {"update": P * (48 * K + 116),                       # 48 B per particle-landmark + 116 B per particle
-           "gather": P * (2 * Nf * 24 + 104),                  # read + write of every pose and landmark row
-           "predict": P * 96, "weights": P * 28, "estimate": P * 12, "add_feature": 0}
+    # algorithmic bytes per launch: update 48 B per particle-landmark + 116 B per particle;
+    # predict 96 B per particle per flush of queued ticks; state resampling 104 B per particle per resample plus 48 B
+    # per particle per landmark row actually re-columned (the reference's eager copy would be 2*Nf*24 B per particle)
     fam_ms = {k: v["ms"] for k, v in fam.items()}
+    alg_total = {"update": P * (48 * K + 116) * fam["update"]["events"],
+                 "predict": P * 96 * fam["predict"]["events"],
+                 "gather": P * (104 * n_resamples + 48 * rows_moved)}
     top = max(("update", "gather", "predict", "weights"), key=lambda k: fam_ms[k])
     roof = {}
     for k in ("update", "gather", "predict"):
         ev = fam[k]["events"]
-        if ev:
-            gbs = alg[k] * ev / (fam_ms[k] * 1e-3) / 1e9
+        if ev and fam_ms[k] > 0:
+            gbs = alg_total[k] / (fam_ms[k] * 1e-3) / 1e9
             roof[k] = {"achieved": gbs, "frac": gbs / peak, "ms_per_event": fam_ms[k] / ev, "events": ev,
-                       "launches": fam[k]["launches"], "alg_bytes_per_event": alg[k]}
-    kern = {"update": "k_fs2_update", "gather": "k_gather_pose + k_gather_rows", "predict": "k_predict",
+                       "launches": fam[k]["launches"], "alg_bytes_per_event": alg_total[k] / ev}
+    kern = {"update": "k_fs2_update_fast", "gather": "k_gather_pose + k_chain + k_materialise_rows",
+            "predict": "k_predict_batch",
             "weights": "scan/search kernels"}[top]
     roofline = {"bound": "hbm", "kernel": kern, "achieved": roof.get(top, {}).get("achieved"), "peak": peak,
                 "unit": "GB/s", "frac": roof.get(top, {}).get("frac"), "traffic": None, "peak_source": peak_src,
@@ -375,7 +383,11 @@ def run_ours(a):
                                        "8 predict ticks per update (BASELINE.json config 4 shape)" % (P, Nf, K),
                            "particles_total": Pg, "parallelism": "particles block-sharded over %d GPU(s)" % world,
                            "resample": "NEFFECTIVE = 0.75 N; gather ran on %.0f%% of timed steps" % (100 * resample_rate),
-                           "l2": "inputs larger than L2 (per-step working set %.1f GB)" % (alg["update"] / 1e9),
+                           "l2": "inputs larger than L2 (the update alone streams %.1f GB per step)"
+                                 % (P * (48 * K + 116) / 1e9),
+                           "map_resampling": "deferred: %d landmark rows re-columned over %d resamples (eager copy: %d)"
+                                             % (rows_moved, n_resamples, n_resamples * Nf),
+                           "predict": "the 8 ticks per step are queued and applied in one pass",
                            "noise": "pre-drawn on the host, %d sets rotated" % NPOOL},
                 "clocks": clk, "gpu_launches": int(launches),
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

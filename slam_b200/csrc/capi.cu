@@ -73,6 +73,8 @@ static int span_end(slamgpu *h, TimedSpan *sp) {
 
 static inline unsigned grid_for(size_t n, int block) { return (unsigned) ((n + block - 1) / block); }
 
+static int flush_predicts(slamgpu *h);
+
 // ---- library-level -------------------------------------------------------------------------------------
 extern "C" const char *slamgpu_last_error(void) { return g_err.c_str(); }
 extern "C" const char *slamgpu_version(void) { return "slamgpu 0.1 sm_100a"; }
@@ -223,6 +225,7 @@ extern "C" void slamgpu_destroy(slamgpu_t *h) { free_all(h); }
 extern "C" int slamgpu_set_stream(slamgpu_t *h, void *s) {
     if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
     CU(cudaSetDevice(h->cfg.device));
+    RET(flush_predicts(h));
     CU(cudaStreamSynchronize(h->stream));
     h->stream = s ? (cudaStream_t) s : h->own_stream;
     return SLAMGPU_OK;
@@ -231,6 +234,7 @@ extern "C" void *slamgpu_get_stream(slamgpu_t *h) { return h ? (void *) h->strea
 extern "C" int slamgpu_synchronize(slamgpu_t *h) {
     if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
     CU(cudaSetDevice(h->cfg.device));
+    RET(flush_predicts(h));
     CU(cudaStreamSynchronize(h->stream));
     return SLAMGPU_OK;
 }
@@ -244,6 +248,22 @@ extern "C" int64_t slamgpu_stat(slamgpu_t *h, int32_t which) {
         case SLAMGPU_STAT_CHAIN_STEPS: return h->stat_chain_steps;
     }
     return 0;
+}
+
+// ---- deferred predict ticks ---------------------------------------------------------------------------------------
+static int flush_predicts(slamgpu *h) {
+    if (h->predict_queue.empty()) return SLAMGPU_OK;
+    PredictBatch b;
+    b.n = (int) h->predict_queue.size();
+    for (int t = 0; t < b.n; t++) b.a[t] = h->predict_queue[t];
+    h->predict_queue.clear();
+    TimedSpan sp;
+    RET(span_begin(h, SLAMGPU_T_PREDICT, &sp));
+    k_predict_batch<<<grid_for(h->P, 256), 256, 0, h->stream>>>(h->soa(h->cur), h->P, b);
+    KCHECK();
+    LAUNCHED(h, SLAMGPU_T_PREDICT);
+    RET(span_end(h, &sp));
+    return SLAMGPU_OK;
 }
 
 // ---- landmark row pool: deferred resampling of the maps (kernels.cuh K7) ---------------------------------------
@@ -340,6 +360,7 @@ extern "C" int slamgpu_upload_particles(slamgpu_t *h, const float *xv, const flo
     if (Nf > h->nf_cap) return slam_fail(SLAMGPU_ECAP, "Nf exceeds nf_cap");
     if (Nf < 0) Nf = (lm_mean || lm_cov) ? h->Nf : -1;  // negative: keep the current landmark count
     CU(cudaSetDevice(h->cfg.device));
+    RET(flush_predicts(h));
     const size_t P = h->P;
     PoseSoA s = h->soa(h->cur);
     if (xv) CU(cudaMemcpyAsync(s.xv, xv, sizeof(float) * 3 * P, cudaMemcpyHostToDevice, h->stream));
@@ -367,6 +388,7 @@ extern "C" int slamgpu_upload_particles_tiled(slamgpu_t *h, int64_t Pt, const fl
     if (Nf < 0 || Nf > h->nf_cap) return slam_fail(SLAMGPU_ECAP, "Nf exceeds nf_cap");
     if (Nf > 0 && (!lm_mean || !lm_cov)) return slam_fail(SLAMGPU_EINVAL, "landmark tile missing");
     CU(cudaSetDevice(h->cfg.device));
+    RET(flush_predicts(h));
     const size_t P = h->P, T = (size_t) Pt;
     const int chunk = 64;  // landmark rows staged per copy
     float *dt = nullptr;
@@ -407,6 +429,7 @@ extern "C" int slamgpu_download_particles(slamgpu_t *h, float *xv, float *Pv, fl
                                           float *lm_cov, int32_t *Nf) {
     if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
     CU(cudaSetDevice(h->cfg.device));
+    RET(flush_predicts(h));
     const size_t P = h->P;
     if (lm_mean || lm_cov) RET(materialise_all(h));
     PoseSoA s = h->soa(h->cur);
@@ -456,7 +479,6 @@ extern "C" int slamgpu_predict(slamgpu_t *h, float V, float G, const float Q[4],
     } else if (h->gauss_staged && h->gauss_rows_staged == 2) {
         dg = h->gauss;
     }
-    if (h->cfg.method == SLAMGPU_FASTSLAM1 && !dg && false) return slam_fail(SLAMGPU_EINVAL, "unreachable");
     PredictArgs a;
     a.V = V; a.G = G; a.dt = dt; a.phi_true = phi_true;
     for (int j = 0; j < 4; j++) a.Q[j] = Q[j];
@@ -464,6 +486,12 @@ extern "C" int slamgpu_predict(slamgpu_t *h, float V, float G, const float Q[4],
     a.sigma_phi = h->cfg.sigma_phi;
     a.method = h->cfg.method;
     a.use_heading = h->cfg.use_heading;
+    if (!dg) {  // no per-particle noise: queue the tick, apply the run of ticks in one pass over the poses
+        h->predict_queue.push_back(a);
+        if (h->predict_queue.size() >= SLAM_PREDICT_QUEUE) RET(flush_predicts(h));
+        return SLAMGPU_OK;
+    }
+    RET(flush_predicts(h));
     TimedSpan sp;
     RET(span_begin(h, SLAMGPU_T_PREDICT, &sp));
     k_predict<<<grid_for(h->P, 256), 256, 0, h->stream>>>(h->soa(h->cur), h->P, a, dg);
@@ -507,6 +535,7 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
     if (h->Nf + Kn > h->nf_cap) return slam_fail(SLAMGPU_ECAP, "landmark capacity (nf_cap) exceeded");
     if (K > 2048 || Kn > 2048) return slam_fail(SLAMGPU_EINVAL, "at most 2048 observations per update (shared-memory staging)");
     CU(cudaSetDevice(h->cfg.device));
+    RET(flush_predicts(h));
     std::vector<int> rows(std::max(K, Kn));
     if (K > 0) {
         std::vector<int> seen(idf, idf + K);
@@ -667,6 +696,8 @@ static int resample_indices(slamgpu *h) {
 static int resample_state(slamgpu *h) {
     const size_t P = h->P, Pg = h->Pg;
     const float new_w = 1.0f / (float) Pg;
+    TimedSpan sg;
+    RET(span_begin(h, SLAMGPU_T_GATHER, &sg));
     h->epoch++;
     h->stat_resamples++;
     int *slot = h->keeplog + (size_t) (h->epoch % h->H) * Pg;
@@ -682,6 +713,7 @@ static int resample_state(slamgpu *h) {
     KCHECK();
     LAUNCHED(h, SLAMGPU_T_GATHER);
     h->cur ^= 1;
+    RET(span_end(h, &sg));
     // background trickle: the stalest rows, enough per resample that no row's backlog reaches the log length
     const int per = (h->Nf + (h->H - 3)) / (h->H - 2);
     std::vector<std::pair<long long, int>> order;
@@ -698,6 +730,7 @@ extern "C" int slamgpu_resample(slamgpu_t *h, const double *unif, int32_t *keep_
                                 int32_t *did_resample) {
     if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
     CU(cudaSetDevice(h->cfg.device));
+    RET(flush_predicts(h));
     if (unif) {
         CU(cudaMemcpyAsync(h->unif(), unif, sizeof(double) * h->P, cudaMemcpyHostToDevice, h->stream));
     } else if (!h->unif_staged) {
@@ -723,10 +756,7 @@ extern "C" int slamgpu_resample(slamgpu_t *h, const double *unif, int32_t *keep_
         CU(cudaStreamSynchronize(h->stream));
     }
     if (did) {
-        TimedSpan sg;
-        RET(span_begin(h, SLAMGPU_T_GATHER, &sg));
         RET(resample_state(h));
-        RET(span_end(h, &sg));
     }
     if (neff) *neff = ne;
     if (did_resample) *did_resample = did ? 1 : 0;
@@ -789,6 +819,7 @@ extern "C" int slamgpu_compute_jacobians_batch(slamgpu_t *h, const int32_t *idf,
                                                float *out) {
     if (!h || !idf || !R || !out || K <= 0) return slam_fail(SLAMGPU_EINVAL, "bad argument");
     CU(cudaSetDevice(h->cfg.device));
+    RET(flush_predicts(h));
     std::vector<int> rows(K);
     std::vector<float> z(2 * (size_t) K, 0.0f);
     for (int i = 0; i < K; i++) {
@@ -818,6 +849,7 @@ extern "C" int slamgpu_compute_jacobians_batch(slamgpu_t *h, const int32_t *idf,
 extern "C" int slamgpu_estimate(slamgpu_t *h, double *x, double *y, double *t) {
     if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
     CU(cudaSetDevice(h->cfg.device));
+    RET(flush_predicts(h));
     TimedSpan sp;
     RET(span_begin(h, SLAMGPU_T_ESTIMATE, &sp));
     PoseSoA s = h->soa(h->cur);
@@ -842,6 +874,7 @@ extern "C" int slamgpu_estimate(slamgpu_t *h, double *x, double *y, double *t) {
 extern "C" int slamgpu_download_decimated(slamgpu_t *h, int64_t stride, float *xv_out, float *lm_out) {
     if (!h || stride <= 0 || !xv_out) return slam_fail(SLAMGPU_EINVAL, "bad argument");
     CU(cudaSetDevice(h->cfg.device));
+    RET(flush_predicts(h));
     const size_t n = (h->P + (size_t) stride - 1) / (size_t) stride;
     float *dx = nullptr;
     float2 *dl = nullptr;
@@ -880,6 +913,7 @@ extern "C" int slamgpu_timing_enable(slamgpu_t *h, int32_t on) {
 extern "C" int slamgpu_timing_read(slamgpu_t *h, int32_t which, double *total_ms, int64_t *events, int64_t *launches) {
     if (!h || which < 0 || which >= SLAMGPU_T_COUNT) return slam_fail(SLAMGPU_EINVAL, "bad argument");
     CU(cudaSetDevice(h->cfg.device));
+    RET(flush_predicts(h));
     RET(timing_flush(h));
     if (total_ms) *total_ms = h->t_ms[which];
     if (events) *events = h->t_events[which];

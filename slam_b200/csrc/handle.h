@@ -59,6 +59,7 @@ struct slamgpu {
     int *anc = nullptr;          // [P] scratch: composed ancestor map
     slam::RowPair *d_pairs = nullptr, *h_pairs = nullptr;  // row-move lists (device / pinned), nf_cap entries
     int *d_phys = nullptr;       // device copy of phys[] for the download helpers
+    std::vector<slam::PredictArgs> predict_queue;  // noise-free predict ticks not yet applied (flush_predicts)
     int64_t stat_rows_moved = 0, stat_resamples = 0, stat_chain_steps = 0;
     cudaStream_t stream = nullptr, own_stream = nullptr;
     float *pose[2] = {nullptr, nullptr};  // each: xv[3][P] then Pv[9][P]

@@ -17,11 +17,6 @@
 
 namespace slam {
 
-struct PredictArgs {
-    float V, G, Q[4], dt, phi_true, wheel_base, sigma_phi;
-    int method, use_heading;
-};
-
 __device__ __forceinline__ void load_pose(const PoseSoA &s, size_t P, size_t p, float *x, float *C) {
 #pragma unroll
     for (int c = 0; c < 3; c++) x[c] = s.xv[c * P + p];
@@ -56,6 +51,29 @@ __global__ void __launch_bounds__(256) k_predict(PoseSoA s, size_t P, PredictArg
     }
     predict_particle(a.method, x, C, a.V, a.G, a.Q, a.dt, a.phi_true, a.wheel_base, a.sigma_phi, a.use_heading != 0,
                      gauss ? g2 : nullptr);
+    store_pose(s, P, p, x, need_cov ? C : nullptr);
+}
+
+// K1 batched: up to SLAM_PREDICT_QUEUE consecutive noise-free predict ticks applied with the pose held in registers:
+// 96 B of traffic per particle for the whole run of ticks instead of per tick.  The host queues ticks
+// (slamgpu_predict returns at once) and flushes the queue before anything else looks at the poses, so callers keep
+// the reference's one-call-per-control-tick loop (fastslam2wrapper.cpp:51-64).
+#define SLAM_PREDICT_QUEUE 16
+struct PredictBatch {
+    PredictArgs a[SLAM_PREDICT_QUEUE];
+    int n;
+};
+__global__ void __launch_bounds__(256) k_predict_batch(PoseSoA s, size_t P, const PredictBatch b) {
+    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    const bool need_cov = (b.a[0].method == 2) || b.a[0].use_heading;
+    float x[3], C[9];
+    load_pose(s, P, p, x, need_cov ? C : nullptr);
+    for (int t = 0; t < b.n; t++) {
+        const PredictArgs &a = b.a[t];
+        predict_particle(a.method, x, C, a.V, a.G, a.Q, a.dt, a.phi_true, a.wheel_base, a.sigma_phi,
+                         a.use_heading != 0, nullptr);
+    }
     store_pose(s, P, p, x, need_cov ? C : nullptr);
 }
 

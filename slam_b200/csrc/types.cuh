@@ -36,6 +36,11 @@ struct RowMoves {  // passed to the kernel by value (512 B): no staging buffer t
     RowPair p[SLAM_MOVES_PER_LAUNCH];
 };
 
+struct PredictArgs {
+    float V, G, Q[4], dt, phi_true, wheel_base, sigma_phi;
+    int method, use_heading;
+};
+
 struct EstPartial {
     double sx, sy;
     float wmax;
