@@ -1,0 +1,133 @@
+"""CPU, world_size 2 over gloo: the EXCHANGE PROTOCOL of the sharded resample reproduces the
+one-piece oracle bit for bit.  Each rank holds half of the weights and runs, in numpy, exactly the steps the CUDA
+library runs per device (slam_b200/csrc/capi.cu: resample_indices): per-1024-block scans locally, block totals
+all-gathered in rank order, the same upper-level scan on every rank, CDF all-gathered, select[] from local uniforms
+with a 2-slot halo from the previous rank, first-exceedance search on running maxima, keep = max(G[c], G[c-1]).
+The device kernels themselves are checked on GPUs by tests/test_gpu_sharded.py."""
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+BLOCK = 1024
+f32 = np.float32
+
+
+def ladder(x):
+    """Hillis-Steele inclusive scan over the last axis (length 32), one fp32 add per step and lane."""
+    x = x.astype(f32).copy()
+    d = 1
+    while d < 32:
+        y = x.copy()
+        y[..., d:] = (x[..., d:] + x[..., :-d]).astype(f32)
+        x = y
+        d *= 2
+    return x
+
+
+def block_scan(x):
+    """Local inclusive scan of consecutive 1024-blocks (zero padded), returns (scan, block totals)."""
+    n = x.size
+    nb = (n + BLOCK - 1) // BLOCK
+    p = np.zeros(nb * BLOCK, f32)
+    p[:n] = x
+    g = ladder(p.reshape(nb, 32, 32))
+    tot = ladder(g[:, :, 31])
+    g[:, 1:, :] = (tot[:, :-1, None] + g[:, 1:, :]).astype(f32)
+    s = g.reshape(-1)[:n]
+    last = np.minimum(np.arange(1, nb + 1) * BLOCK, n) - 1
+    return s, s[last].copy()
+
+
+def upper_scan(tot):
+    """The recursive levels over a totals array: returns (scanned totals, blocked sum of the level below)."""
+    s, t2 = block_scan(tot)
+    if t2.size > 1:
+        s2, _ = upper_scan(t2)
+        for b in range(1, t2.size):
+            s[b * BLOCK:(b + 1) * BLOCK] = (s2[b - 1] + s[b * BLOCK:(b + 1) * BLOCK]).astype(f32)
+    total = f32(s[-2] + tot[-1]) if tot.size > 1 else f32(tot[0])
+    return s, total
+
+
+def allgather(x):
+    out = [torch.empty_like(torch.from_numpy(x)) for _ in range(dist.get_world_size())]
+    dist.all_gather(out, torch.from_numpy(np.ascontiguousarray(x)))
+    return np.concatenate([o.numpy() for o in out])
+
+
+def worker(rank, world, port, P_local, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    Pg = P_local * world
+    rng = np.random.default_rng(99)                      # every rank draws the same global inputs, uses its slice
+    w_all = (rng.random(Pg) ** 5).astype(f32)
+    u_all = rng.random(Pg)
+    sl = slice(rank * P_local, (rank + 1) * P_local)
+    w, u = w_all[sl], u_all[sl]
+    # A/B: totals of w -> ws
+    _, tot = block_scan(w)
+    _, ws = upper_scan(allgather(tot))
+    # C/D: normalise, local cdf scan, totals of cdf and of w^2
+    wn = (w / ws).astype(f32)
+    sq = (wn * wn).astype(f32)
+    cdf_loc, tot_c = block_scan(wn)
+    _, tot_s = block_scan(sq)
+    tc_scanned, _ = upper_scan(allgather(tot_c))
+    _, s2 = upper_scan(allgather(tot_s))
+    neff = f32(1.0) / s2
+    # E: final cdf for the local blocks, all-gathered
+    b0 = rank * P_local // BLOCK
+    cdf = cdf_loc.copy()
+    for b in range(P_local // BLOCK):
+        gb = b0 + b
+        if gb > 0:
+            cdf[b * BLOCK:(b + 1) * BLOCK] = (tc_scanned[gb - 1] + cdf[b * BLOCK:(b + 1) * BLOCK]).astype(f32)
+    cdf_g = allgather(cdf)
+    M = np.maximum.accumulate(cdf_g)
+    # F: select for local slots (+2 halo from the previous rank), search, keep
+    k = f32(1.0 / f32(Pg))
+    di = np.zeros(Pg, f32)
+    t = f32(k / f32(2))
+    for i in range(Pg):
+        di[i] = t
+        t = f32(t + k)
+    lo = max(0, rank * P_local - 2)
+    sel = (di[lo:(rank + 1) * P_local].astype(np.float64) + u_all[lo:(rank + 1) * P_local] * np.float64(k)
+           - np.float64(f32(k / f32(2)))).astype(f32)
+    G = np.searchsorted(M, sel, side="right")        # first index with M > sel
+    halo = rank * P_local - lo
+    keep = G[halo:].copy()
+    prev = np.concatenate([[-1] * (2 - halo), G])[1:1 + P_local] if halo < 2 else G[1:1 + P_local]
+    keep = np.maximum(keep, prev)
+    keep = np.where(keep >= Pg, -1, keep).astype(np.int32)
+    q.put((rank, keep, float(neff), wn))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("P_local", [2048])
+def test_two_rank_protocol_equals_one_piece_oracle(oracle, P_local):
+    world, port = 2, 29611
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=worker, args=(r, world, port, P_local, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = sorted([q.get(timeout=120) for _ in range(world)], key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    Pg = P_local * world
+    rng = np.random.default_rng(99)
+    w_all = (rng.random(Pg) ** 5).astype(f32)
+    u_all = rng.random(Pg)
+    wn_o, keep_o, neff_o = oracle.resample_indices(w_all, u_all, scan_mode=1)
+    keep = np.concatenate([g[1] for g in got])
+    wn = np.concatenate([g[3] for g in got])
+    assert np.array_equal(wn, wn_o)
+    assert all(g[2] == float(neff_o) for g in got)
+    assert np.array_equal(keep, keep_o)
