@@ -102,7 +102,7 @@ static void free_all(slamgpu *h) {
     for (auto e : h->free_events) cudaEventDestroy(e);
     void *dev[] = {h->pose[0], h->pose[1], h->w, h->lm_mean, h->lm_cov, h->gauss, h->unif_base, h->di_base, h->cdf,
                    h->mloc, h->sel, h->keep, h->tot_w, h->tot_c, h->tot_s, h->bmax, h->d_sc, h->d_z, h->d_row,
-                   h->d_rec_in, h->d_rec_out, h->d_est, h->keeplog, h->anc, h->d_phys};
+                   h->d_rec_in, h->d_rec_out, h->d_est, h->keeplog, h->anc, h->d_phys, h->fb_list, h->fb_count};
     for (void *p : dev)
         if (p) cudaFree(p);
     if (h->h_sc) cudaFreeHost(h->h_sc);
@@ -163,6 +163,8 @@ static int create_impl(const slamgpu_config *cfg, slamgpu *h) {
     CU(cudaMalloc(&h->lm_mean, sizeof(float2) * (size_t) h->rows_total * P));
     CU(cudaMalloc(&h->lm_cov, sizeof(float4) * (size_t) h->rows_total * P));
     CU(cudaMalloc(&h->anc, sizeof(int) * P));
+    CU(cudaMalloc(&h->fb_list, sizeof(int) * P));
+    CU(cudaMalloc(&h->fb_count, sizeof(int)));
     CU(cudaMalloc(&h->d_phys, sizeof(int) * h->nf_cap));
     CU(cudaMalloc(&h->gauss, sizeof(float) * 3 * P));
     CU(cudaMalloc(&h->unif_base, sizeof(double) * (P + 2)));
@@ -570,9 +572,15 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
         RET(span_begin(h, SLAMGPU_T_UPDATE, &sp));
         const bool fast = h->cfg.math_mode == SLAMGPU_MATH_FAST;
         const size_t smem_fast = SLAM_OBS_OFF_SMEM(K);
-        if (fs2 && fast)
-            k_fs2_update_fast<<<grid_for(P, 128), 128, smem_fast, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, dg);
-        else if (fs2)
+        if (fs2 && fast) {
+            CU(cudaMemsetAsync(h->fb_count, 0, sizeof(int), h->stream));
+            k_fs2_update_fast<<<grid_for(P, SLAM_UPDATE_THREADS), SLAM_UPDATE_THREADS, SLAM_FS2_FAST_SMEM(K), h->stream>>>(
+                h->soa(h->cur), h->ring(), P, o, K, Rm, dg, h->fb_list, h->fb_count);
+            KCHECK();
+            LAUNCHED(h, SLAMGPU_T_UPDATE);
+            k_fs2_update_listed<<<std::min<unsigned>(grid_for(P, 128), 148u * 4u), 128, smem_fast, h->stream>>>(
+                h->soa(h->cur), h->ring(), P, o, K, Rm, dg, h->fb_list, h->fb_count);
+        } else if (fs2)
             k_fs2_update<<<grid_for(P, 128), 128, smem, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, dg);
         else if (fast)
             k_fs1_update_fast<<<grid_for(P, 256), 256, smem_fast, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm);

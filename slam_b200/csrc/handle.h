@@ -57,6 +57,7 @@ struct slamgpu {
     int H = 0;                   // epochs of keep[] kept in the log
     int *keeplog = nullptr;      // [H][Pg] global keep arrays, epoch e at slot e % H
     int *anc = nullptr;          // [P] scratch: composed ancestor map
+    int *fb_list = nullptr, *fb_count = nullptr;  // [P], [1]: particles the fast FastSLAM2 kernel hands to the reference-order one
     slam::RowPair *d_pairs = nullptr, *h_pairs = nullptr;  // row-move lists (device / pinned), nf_cap entries
     int *d_phys = nullptr;       // device copy of phys[] for the download helpers
     std::vector<slam::PredictArgs> predict_queue;  // noise-free predict ticks not yet applied (flush_predicts)

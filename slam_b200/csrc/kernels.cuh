@@ -174,12 +174,14 @@ __device__ __forceinline__ void lm_load_at(const float2 *mp, const float4 *cp, f
     Pf[0] = c.x; Pf[1] = c.z; Pf[2] = c.y; Pf[3] = c.w;
 }
 
-// K3 (fast formulation, SLAMGPU_MATH_FAST): same kernel structure, ~3.5x fewer instructions (slam_math.cuh).
-// A particle whose pose covariance is not numerically positive definite takes the reference-order routine, kept
-// out of line so that it costs the common path nothing but a branch.
-__device__ __noinline__ void fs2_update_particle_reference_order(PoseSoA s, MapRing m, size_t P, size_t p,
-                                                                 const float2 *sz, const unsigned long long *soff,
-                                                                 int K, float4 Rm, const float *gauss) {
+// K3 (fast formulation, SLAMGPU_MATH_FAST): same kernel structure, ~4x fewer instructions (slam_math.cuh).
+// A particle whose pose covariance is not numerically positive definite (e.g. Pv == 0 right after a pose sample)
+// is NOT processed by the fast kernel: its index goes to a list and k_fs2_update_listed, launched right behind,
+// gives it the reference-order routine (so Eigen's behaviour on a failed LLT is still reproduced).  Keeping that
+// routine out of the fast kernel keeps its ~80 registers out of the fast kernel's allocation.
+__device__ __forceinline__ void fs2_update_particle_reference_order(PoseSoA s, MapRing m, size_t P, size_t p,
+                                                                    const float2 *sz, const unsigned long long *soff,
+                                                                    int K, float4 Rm, const float *gauss) {
     const float R[4] = {Rm.x, Rm.y, Rm.z, Rm.w};
     float x[3], C[9], x0[3], C0[9];
     load_pose(s, P, p, x, C);
@@ -225,60 +227,131 @@ __device__ __forceinline__ void stage_obs_off(const ObsSet &o, int K, size_t P, 
 }
 #define SLAM_OBS_OFF_SMEM(K) ((sizeof(unsigned long long) + sizeof(float2)) * ((K) + 1))
 
-__global__ void __launch_bounds__(128) k_fs2_update_fast(PoseSoA s, MapRing m, size_t P, ObsSet o, int K, float4 Rm,
-                                                         const float *__restrict__ gauss) {
+__global__ void __launch_bounds__(128) k_fs2_update_listed(PoseSoA s, MapRing m, size_t P, ObsSet o, int K, float4 Rm,
+                                                           const float *__restrict__ gauss,
+                                                           const int *__restrict__ list, const int *__restrict__ count) {
     float2 *sz;
     unsigned long long *soff;
     stage_obs_off(o, K, P, sz, soff);
+    const int n = *count;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        fs2_update_particle_reference_order(s, m, P, (size_t) list[i], sz, soff, K, Rm, gauss);
+}
+
+// Per-thread asynchronous landmark ring.  Each thread copies ITS OWN column of the next landmark rows from HBM into its
+// own shared-memory slots with cp.async (LDGSTS) and reads them back later: shared memory serves as a per-thread
+// extension of the register file for loads in flight, so the prefetch depth (SLAM_RING_DEPTH rows = 24 B x depth per
+// thread, ~64 KB in flight per SM) no longer costs registers and no CTA-wide barrier is needed (nobody reads
+// another thread's slot).  With one row in flight per thread the kernel sat on long-scoreboard stalls at 58 % of the
+// HBM peak (ncu r01 v2, profiles/).
+#define SLAM_RING_DEPTH 4
+#define SLAM_UPDATE_THREADS 128
+__device__ __forceinline__ void cp_async_8(void *smem_dst, const void *gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned) __cvta_generic_to_shared(smem_dst)), "l"(gsrc)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_16(void *smem_dst, const void *gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned) __cvta_generic_to_shared(smem_dst)), "l"(gsrc)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+#define SLAM_FS2_FAST_SMEM(K) \
+    ((sizeof(float4) + sizeof(float2)) * SLAM_RING_DEPTH * SLAM_UPDATE_THREADS + SLAM_OBS_OFF_SMEM(K))
+
+__global__ void __launch_bounds__(SLAM_UPDATE_THREADS) k_fs2_update_fast(PoseSoA s, MapRing m, size_t P, ObsSet o, int K,
+                                                                         float4 Rm, const float *__restrict__ gauss,
+                                                                         int *__restrict__ list, int *__restrict__ count) {
+    constexpr int D = SLAM_RING_DEPTH, T = SLAM_UPDATE_THREADS;
+    float4 *const ring_cov = reinterpret_cast<float4 *>(slam_smem) + threadIdx.x;                // slot s at [s * T]
+    float2 *const ring_mean = reinterpret_cast<float2 *>(reinterpret_cast<float4 *>(slam_smem) + D * T) + threadIdx.x;
+    unsigned long long *const soff = reinterpret_cast<unsigned long long *>(
+        slam_smem + (sizeof(float4) + sizeof(float2)) * D * T);
+    float2 *const sz = reinterpret_cast<float2 *>(soff + (K + 1));
+    for (int i = threadIdx.x; i < K; i += blockDim.x) {
+        sz[i] = o.z[i];
+        soff[i] = (unsigned long long) o.row[i] * (unsigned long long) P;
+    }
+    __syncthreads();
     const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= P) return;
+    const float2 *const mean_p = m.mean + p;
+    const float4 *const cov_p = m.cov + p;
+    // the first D-1 rows go in flight before anything else is looked at
+#pragma unroll
+    for (int j = 0; j < D - 1; j++) {
+        if (j < K) {
+            cp_async_8(ring_mean + j * T, mean_p + soff[j]);
+            cp_async_16(ring_cov + j * T, cov_p + soff[j]);
+        }
+        cp_async_commit();
+    }
     const float R[4] = {Rm.x, Rm.y, Rm.z, Rm.w};
     float x[3], x0[3], C0[9], L0[6];
     load_pose(s, P, p, x0, C0);
     ProposalInfo pi;
     if (!proposal_begin_fast(C0, L0, pi)) {
-        fs2_update_particle_reference_order(s, m, P, p, sz, soff, K, Rm, gauss);
+        list[atomicAdd(count, 1)] = (int) p;
+        cp_async_wait<0>();
         return;
     }
 #pragma unroll
     for (int j = 0; j < 3; j++) x[j] = x0[j];
-    const float g3[3] = {gauss[p], gauss[P + p], gauss[2 * P + p]};
-    const float wgt = s.w[p];
-    float2 *const mean_p = m.mean + p;
-    float4 *const cov_p = m.cov + p;
 
-    // pass 1: proposal (read only), the next landmark is in flight while this one is processed
-    float xf[2], Pf[4], nxf[2], nPf[4];
-    lm_load_at(mean_p + soff[0], cov_p + soff[0], nxf, nPf);
-    for (int i = 0; i < K; i++) {
-        xf[0] = nxf[0]; xf[1] = nxf[1];
+    // pass 1: proposal (read only), sequential over the observations (fastslam2.cpp:314-350); row i sits in slot i % D
+    float xf[2], Pf[4];
+    for (int i0 = 0; i0 < K; i0 += D) {
 #pragma unroll
-        for (int j = 0; j < 4; j++) Pf[j] = nPf[j];
-        const unsigned long long noff = soff[i + 1];
-        lm_load_at(mean_p + noff, cov_p + noff, nxf, nPf);
-        const float z[2] = {sz[i].x, sz[i].y};
-        proposal_step_fast(x, pi, R, xf, Pf, z);
+        for (int sl = 0; sl < D; sl++) {
+            const int i = i0 + sl;
+            if (i < K) {
+                const int j = i + D - 1;
+                if (j < K) {
+                    const unsigned long long noff = soff[j];
+                    cp_async_8(ring_mean + ((sl + D - 1) % D) * T, mean_p + noff);
+                    cp_async_16(ring_cov + ((sl + D - 1) % D) * T, cov_p + noff);
+                }
+                cp_async_commit();
+                cp_async_wait<D - 1>();  // one group per row: all but the newest D-1 have landed, row i among them
+                lm_load_at(ring_mean + sl * T, ring_cov + sl * T, xf, Pf);
+                const float z[2] = {sz[i].x, sz[i].y};
+                proposal_step_fast(x, pi, R, xf, Pf, z);
+            }
+        }
     }
+    const float g3[3] = {gauss[p], gauss[P + p], gauss[2 * P + p]};
     float xs[3];
     const float ratio = proposal_finish_fast(x0, L0, x, pi, g3, xs);
 
-    // pass 2: likelihood at the sampled pose + landmark EKF, written back in place
+    // pass 2: likelihood at the sampled pose + landmark EKF, written back in place.  The observations are independent
+    // here, so they are walked BACKWARDS: the last D rows of pass 1 are still in the ring, and the rows read most
+    // recently are the ones most likely still in L2 (a forward walk is the LRU worst case).
     float like = 1.0f;
-    unsigned long long off = soff[0];
-    lm_load_at(mean_p + off, cov_p + off, nxf, nPf);
-    for (int i = 0; i < K; i++) {
-        xf[0] = nxf[0]; xf[1] = nxf[1];
+    for (int i0 = ((K - 1) / D) * D; i0 >= 0; i0 -= D) {
 #pragma unroll
-        for (int j = 0; j < 4; j++) Pf[j] = nPf[j];
-        const unsigned long long noff = soff[i + 1];
-        lm_load_at(mean_p + noff, cov_p + noff, nxf, nPf);  // i == K-1 re-reads row K-1 before its store: harmless
-        const float z[2] = {sz[i].x, sz[i].y};
-        like = like * likelihood_and_feature_update_fast(xs, R, xf, Pf, z);
-        __stcs(mean_p + off, make_float2(xf[0], xf[1]));
-        __stcs(cov_p + off, make_float4(Pf[0], Pf[2], Pf[1], Pf[3]));
-        off = noff;
+        for (int sl = D - 1; sl >= 0; sl--) {
+            const int i = i0 + sl;
+            if (i < K) {
+                cp_async_wait<D - 1>();
+                lm_load_at(ring_mean + sl * T, ring_cov + sl * T, xf, Pf);
+                const unsigned long long off = soff[i];
+                if (i - D >= 0) {  // the slot just read takes row i - D
+                    const unsigned long long noff = soff[i - D];
+                    cp_async_8(ring_mean + sl * T, mean_p + noff);
+                    cp_async_16(ring_cov + sl * T, cov_p + noff);
+                }
+                cp_async_commit();
+                const float z[2] = {sz[i].x, sz[i].y};
+                like = like * likelihood_and_feature_update_fast(xs, R, xf, Pf, z);
+                __stcs(m.mean + p + off, make_float2(xf[0], xf[1]));
+                __stcs(m.cov + p + off, make_float4(Pf[0], Pf[2], Pf[1], Pf[3]));
+            }
+        }
     }
-    s.w[p] = wgt * like * ratio;
+    s.w[p] = s.w[p] * like * ratio;
     const float Z[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
     store_pose(s, P, p, xs, Z);
 }

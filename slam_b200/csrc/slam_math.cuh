@@ -416,15 +416,35 @@ SLAM_HD void fs1_weight_and_feature_update(const float *x, const float *R, float
 // Differences from the reference are rounding-level (a few ulp per operation); tests bound them against the oracle
 // with the same tolerances as the reference-order path.
 // =============================================================================================================
+// MUFU approximations issued directly (rsqrt/rcp/ex2 .approx.ftz): rsqrtf(), __fdividef() and __expf() without
+// -ftz wrap the same MUFU instruction in a denormal-range test and two rescaling multiplies (3-5 extra instructions
+// each, 11 such calls per particle-landmark: ncu r01, profiles/).  Denormal inputs cannot occur here (ranges,
+// variances and determinants of metre-scale quantities); a likelihood factor below 2^-126 flushes to zero.
 #if defined(__CUDA_ARCH__)
-#define SLAM_RSQRT(x) rsqrtf(x)
-#define SLAM_RCP(x) __fdividef(1.0f, (x))
-#define SLAM_EXP(x) __expf(x)
+__device__ __forceinline__ float mufu_rsqrt(float x) {
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float mufu_rcp(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float mufu_ex2(float x) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+#define SLAM_RSQRT(x) mufu_rsqrt(x)
+#define SLAM_RCP(x) mufu_rcp(x)
+#define SLAM_EXP2(x) mufu_ex2(x)
 #else
 #define SLAM_RSQRT(x) (1.0f / sqrtf(x))
 #define SLAM_RCP(x) (1.0f / (x))
-#define SLAM_EXP(x) expf(x)
+#define SLAM_EXP2(x) exp2f(x)
 #endif
+#define SLAM_NEG_HALF_LOG2E (-0.72134752f)  // exp(-q/2) == exp2(q * -0.5*log2(e))
 
 #define SLAM_INV_TWO_PI 0.159154943f
 
@@ -458,10 +478,12 @@ SLAM_HD float wrap_fast(float t) {
 }
 
 // computeJacobians (core.cpp:666-713) for one landmark: predicted range zp[0], UNWRAPPED predicted bearing zp[1] =
-// atan2(dy,dx) - theta (the caller wraps the innovation once), Hf and the symmetrised innovation
-// covariance S = Hf Pf Hf' + R as (s00, s10, s11).  Pf row-major, may be asymmetric.
+// atan2(dy,dx) - theta (the caller wraps the innovation once), Hf, T = Hf * sym(Pf) (row-major; its transpose is the
+// PHt of choleskyUpdate) and the symmetrised innovation covariance S = Hf Pf Hf' + R as (s00, s10, s11).
+// (S + S')/2 == Hf sym(Pf) Hf' + sym(R) exactly, so the stored Pf (row-major, off-diagonals possibly an ulp apart —
+// the reference never symmetrises P, core.cpp:290) enters through pm = (Pf01 + Pf10)/2 and S needs 3 entries, not 4.
 SLAM_HD void jacobian_fast(const float *xv, const float *R, const float *xf, const float *Pf, float *zp, float *Hf,
-                           float *S3) {
+                           float *T, float *S3) {
     const float dx = xf[0] - xv[0];
     const float dy = xf[1] - xv[1];
     const float d2 = fmaf(dx, dx, dy * dy);
@@ -475,15 +497,14 @@ SLAM_HD void jacobian_fast(const float *xv, const float *R, const float *xf, con
     Hf[1] = dy * rd;
     Hf[2] = -dy * rd2;
     Hf[3] = dx * rd2;
-    const float t00 = fmaf(Hf[0], Pf[0], Hf[1] * Pf[2]), t01 = fmaf(Hf[0], Pf[1], Hf[1] * Pf[3]);
-    const float t10 = fmaf(Hf[2], Pf[0], Hf[3] * Pf[2]), t11 = fmaf(Hf[2], Pf[1], Hf[3] * Pf[3]);
-    const float s00 = fmaf(t00, Hf[0], t01 * Hf[1]) + R[0];
-    const float s01 = fmaf(t00, Hf[2], t01 * Hf[3]) + R[1];
-    const float s10 = fmaf(t10, Hf[0], t11 * Hf[1]) + R[2];
-    const float s11 = fmaf(t10, Hf[2], t11 * Hf[3]) + R[3];
-    S3[0] = s00;
-    S3[1] = 0.5f * (s01 + s10);
-    S3[2] = s11;
+    const float pm = 0.5f * (Pf[1] + Pf[2]), rm = 0.5f * (R[1] + R[2]);
+    T[0] = fmaf(Hf[0], Pf[0], Hf[1] * pm);
+    T[1] = fmaf(Hf[0], pm, Hf[1] * Pf[3]);
+    T[2] = fmaf(Hf[2], Pf[0], Hf[3] * pm);
+    T[3] = fmaf(Hf[2], pm, Hf[3] * Pf[3]);
+    S3[0] = fmaf(T[0], Hf[0], fmaf(T[1], Hf[1], R[0]));
+    S3[1] = fmaf(T[0], Hf[2], fmaf(T[1], Hf[3], rm));
+    S3[2] = fmaf(T[2], Hf[2], fmaf(T[3], Hf[3], R[3]));
 }
 
 // Lower Cholesky factor of a symmetric 3x3 given as (a00, a10, a11, a20, a21, a22), in reciprocal-diagonal form:
@@ -532,8 +553,8 @@ struct ProposalInfo {
 // One observation of FastSLAM2::sampleProposal (fastslam2.cpp:314-350) in information form.
 SLAM_HD void proposal_step_fast(float *x, ProposalInfo &pi, const float *R, const float *xf, const float *Pf,
                                 const float *z) {
-    float zp[2], Hf[4], S[3];
-    jacobian_fast(x, R, xf, Pf, zp, Hf, S);
+    float zp[2], Hf[4], T[4], S[3];
+    jacobian_fast(x, R, xf, Pf, zp, Hf, T, S);
     const float v0 = z[0] - zp[0], v1 = wrap_fast(z[1] - zp[1]);
     // G = S^-1 (symmetric): adjugate / det
     const float rdet = SLAM_RCP(fmaf(S[0], S[2], -S[1] * S[1]));
@@ -565,8 +586,8 @@ SLAM_HD void proposal_step_fast(float *x, ProposalInfo &pi, const float *R, cons
 SLAM_HD float gauss3_from_factor(const float *L, const float *v) {
     float nin[3];
     chol3_fwd(L, v, nin);
-    const float E = -0.5f * fmaf(nin[0], nin[0], fmaf(nin[1], nin[1], nin[2] * nin[2]));
-    return SLAM_EXP(E) * (SLAM_INV_TWO_PI * L[0] * L[2] * L[5]);
+    const float q = fmaf(nin[0], nin[0], fmaf(nin[1], nin[1], nin[2] * nin[2]));
+    return SLAM_EXP2(q * SLAM_NEG_HALF_LOG2E) * (SLAM_INV_TWO_PI * L[0] * L[2] * L[5]);
 }
 
 // Per-particle prologue: factor Pv0 once; gives Lambda0 = Pv0^-1 and the factor for the prior density.
@@ -605,19 +626,18 @@ SLAM_HD float proposal_finish_fast(const float *x0, const float *L0, const float
 // (featureUpdate -> choleskyUpdate, core.cpp:132-175,275-291), sharing one factorisation of S.
 SLAM_HD float likelihood_and_feature_update_fast(const float *xs, const float *R, float *xf, float *Pf,
                                                  const float *z) {
-    float zp[2], Hf[4], S[3];
-    jacobian_fast(xs, R, xf, Pf, zp, Hf, S);
+    float zp[2], Hf[4], T[4], S[3];
+    jacobian_fast(xs, R, xf, Pf, zp, Hf, T, S);
     const float v0 = z[0] - zp[0], v1 = wrap_fast(z[1] - zp[1]);
     const float l00i = SLAM_RSQRT(S[0]);
     const float l10 = S[1] * l00i;
     const float l11i = SLAM_RSQRT(fmaf(-l10, l10, S[2]));
     const float n0 = v0 * l00i;
     const float n1 = fmaf(-l10, n0, v1) * l11i;
-    const float E = -0.5f * fmaf(n0, n0, n1 * n1);
-    const float like = SLAM_EXP(E) * (SLAM_INV_TWO_PI * l00i * l11i);
-    // PHt = Pf Hf'
-    const float p00 = fmaf(Pf[0], Hf[0], Pf[1] * Hf[1]), p01 = fmaf(Pf[0], Hf[2], Pf[1] * Hf[3]);
-    const float p10 = fmaf(Pf[2], Hf[0], Pf[3] * Hf[1]), p11 = fmaf(Pf[2], Hf[2], Pf[3] * Hf[3]);
+    const float q = fmaf(n0, n0, n1 * n1);
+    const float like = SLAM_EXP2(q * SLAM_NEG_HALF_LOG2E) * (SLAM_INV_TWO_PI * l00i * l11i);
+    // PHt = Pf Hf' = (Hf Pf)' = T' (Pf through its symmetric part, see jacobian_fast)
+    const float p00 = T[0], p01 = T[2], p10 = T[1], p11 = T[3];
     // W1 = PHt * U^-1, U = L' = [l00 l10; 0 l11]
     const float w00 = p00 * l00i, w10 = p10 * l00i;
     const float w01 = fmaf(-w00, l10, p01) * l11i, w11 = fmaf(-w10, l10, p11) * l11i;
