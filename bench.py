@@ -326,6 +326,7 @@ def run_ours(a):
     stats1 = f.stats()
     rows_moved = stats1["rows_moved"] - stats0["rows_moved"]
     n_resamples = stats1["resamples"] - stats0["resamples"]
+    rows_fused = stats1["rows_fused"] - stats0["rows_fused"]
     fam = f.timing_read()
     f.timing_enable(False)
     resample_rate = state["resamples"] / max(1, state["steps"])
@@ -354,7 +355,7 @@ def run_ours(a):
     fam_ms = {k: v["ms"] for k, v in fam.items()}
     alg_total = {"update": P * (48 * K + 116) * fam["update"]["events"],
                  "predict": P * 96 * fam["predict"]["events"],
-                 "gather": P * (104 * n_resamples + 48 * rows_moved)}
+                 "gather": P * (104 * n_resamples + 48 * (rows_moved - rows_fused))}
     top = max(("update", "gather", "predict", "weights"), key=lambda k: fam_ms[k])
     roof = {}
     for k in ("update", "gather", "predict"):
@@ -363,8 +364,8 @@ def run_ours(a):
             gbs = alg_total[k] / (fam_ms[k] * 1e-3) / 1e9
             roof[k] = {"achieved": gbs, "frac": gbs / peak, "ms_per_event": fam_ms[k] / ev, "events": ev,
                        "launches": fam[k]["launches"], "alg_bytes_per_event": alg_total[k] / ev}
-    kern = {"update": "k_fs2_update_fast", "gather": "k_gather_pose + k_chain + k_materialise_rows",
-            "predict": "k_predict_batch",
+    kern = {"update": "k_fs2_update_fast<REMAP> (cp.async landmark ring)", "gather": "k_gather_pose + k_chain + k_materialise_rows",
+            "predict": "k_predict_batch_fast",
             "weights": "scan/search kernels"}[top]
     roofline = {"bound": "hbm", "kernel": kern, "achieved": roof.get(top, {}).get("achieved"), "peak": peak,
                 "unit": "GB/s", "frac": roof.get(top, {}).get("frac"), "traffic": None, "peak_source": peak_src,
@@ -385,8 +386,9 @@ def run_ours(a):
                            "resample": "NEFFECTIVE = 0.75 N; gather ran on %.0f%% of timed steps" % (100 * resample_rate),
                            "l2": "inputs larger than L2 (the update alone streams %.1f GB per step)"
                                  % (P * (48 * K + 116) / 1e9),
-                           "map_resampling": "deferred: %d landmark rows re-columned over %d resamples (eager copy: %d)"
-                                             % (rows_moved, n_resamples, n_resamples * Nf),
+                           "map_resampling": "deferred: %d landmark rows re-columned over %d resamples (eager copy: %d); "
+                                             "%d of them inside the update kernel itself (fused, no extra pass)"
+                                             % (rows_moved, n_resamples, n_resamples * Nf, rows_fused),
                            "predict": "the 8 ticks per step are queued and applied in one pass",
                            "noise": "pre-drawn on the host, %d sets rotated" % NPOOL},
                 "clocks": clk, "gpu_launches": int(launches),

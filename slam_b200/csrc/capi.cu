@@ -100,8 +100,10 @@ static void free_all(slamgpu *h) {
         cudaEventDestroy(sp.b);
     }
     for (auto e : h->free_events) cudaEventDestroy(e);
+    for (auto e : h->obs_ev)
+        if (e) cudaEventDestroy(e);
     void *dev[] = {h->pose[0], h->pose[1], h->w, h->lm_mean, h->lm_cov, h->gauss, h->unif_base, h->di_base, h->cdf,
-                   h->mloc, h->sel, h->keep, h->tot_w, h->tot_c, h->tot_s, h->bmax, h->d_sc, h->d_z, h->d_row,
+                   h->mloc, h->sel, h->keep, h->tot_w, h->tot_c, h->tot_s, h->bmax, h->d_sc, h->d_z,
                    h->d_rec_in, h->d_rec_out, h->d_est, h->keeplog, h->anc, h->d_phys, h->fb_list, h->fb_count};
     for (void *p : dev)
         if (p) cudaFree(p);
@@ -176,10 +178,16 @@ static int create_impl(const slamgpu_config *cfg, slamgpu *h) {
     h->est_blocks = 148 * 4;
     CU(cudaMalloc(&h->d_est, sizeof(EstPartial) * (h->est_blocks + 1)));
     CU(cudaHostAlloc(&h->h_est, sizeof(EstPartial), cudaHostAllocDefault));
+    {   // the FastSLAM2 fast kernels stage up to 2048 observations next to their landmark ring: > 48 KB
+        const int big = (int) SLAM_FS2_FAST_SMEM(2048);
+        CU(cudaFuncSetAttribute(k_fs2_update_fast<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        CU(cudaFuncSetAttribute(k_fs2_update_fast<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        CU(cudaFuncSetAttribute(k_fs2_update_listed<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        CU(cudaFuncSetAttribute(k_fs2_update_listed<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+    }
     h->obs_cap = 1024;
-    CU(cudaMalloc(&h->d_z, sizeof(float2) * h->obs_cap));
-    CU(cudaMalloc(&h->d_row, sizeof(int) * h->obs_cap));
-    CU(cudaHostAlloc(&h->h_obs, (sizeof(float2) + sizeof(int)) * h->obs_cap, cudaHostAllocDefault));
+    CU(cudaMalloc(&h->d_z, (sizeof(float2) + 2 * sizeof(int)) * h->obs_cap));
+    CU(cudaHostAlloc(&h->h_obs, (sizeof(float2) + 2 * sizeof(int)) * h->obs_cap * SLAM_OBS_SLOTS, cudaHostAllocDefault));
     // ParticleSLAMWrapper::initializeParticles (ParticleSLAMWrapper.cpp:17-25): w = 1/N, xv = 0, Pv = 0
     CU(cudaMemsetAsync(h->pose[0], 0, sizeof(float) * 12 * P, h->stream));
     CU(cudaMemsetAsync(h->unif_base, 0, sizeof(double) * (P + 2), h->stream));
@@ -248,6 +256,7 @@ extern "C" int64_t slamgpu_stat(slamgpu_t *h, int32_t which) {
         case SLAMGPU_STAT_ROWS_MOVED: return h->stat_rows_moved;
         case SLAMGPU_STAT_RESAMPLES: return h->stat_resamples;
         case SLAMGPU_STAT_CHAIN_STEPS: return h->stat_chain_steps;
+        case SLAMGPU_STAT_ROWS_FUSED: return h->stat_rows_fused;
     }
     return 0;
 }
@@ -261,7 +270,27 @@ static int flush_predicts(slamgpu *h) {
     h->predict_queue.clear();
     TimedSpan sp;
     RET(span_begin(h, SLAMGPU_T_PREDICT, &sp));
-    k_predict_batch<<<grid_for(h->P, 256), 256, 0, h->stream>>>(h->soa(h->cur), h->P, b);
+    if (h->cfg.math_mode == SLAMGPU_MATH_FAST) {
+        PredictBatchFast f;
+        f.n = b.n;
+        f.with_cov = b.a[0].method == 2;
+        f.use_heading = b.a[0].use_heading;
+        for (int t = 0; t < b.n; t++) {
+            const PredictArgs &a = b.a[t];
+            PredictTick &k = f.t[t];
+            k.vdt = a.V * a.dt;
+            k.dt = a.dt;
+            k.dtheta = a.V * a.dt * sinf(a.G / a.wheel_base);  // the reference's sin(G/WB), fastslam2.cpp:103
+            k.G = a.G;
+            k.gu20 = a.dt * sinf(a.G) / a.wheel_base;
+            k.gu21 = a.V * a.dt * cosf(a.G) / a.wheel_base;
+            for (int j = 0; j < 4; j++) k.Q[j] = a.Q[j];
+            k.phi_true = a.phi_true;
+            k.R_phi = a.sigma_phi * a.sigma_phi;
+        }
+        k_predict_batch_fast<<<grid_for(h->P, 256), 256, 0, h->stream>>>(h->soa(h->cur), h->P, f);
+    } else
+        k_predict_batch<<<grid_for(h->P, 256), 256, 0, h->stream>>>(h->soa(h->cur), h->P, b);
     KCHECK();
     LAUNCHED(h, SLAMGPU_T_PREDICT);
     RET(span_end(h, &sp));
@@ -504,29 +533,86 @@ extern "C" int slamgpu_predict(slamgpu_t *h, float V, float G, const float Q[4],
 }
 
 // ---- update, per-particle part -----------------------------------------------------------------------------
-static int stage_obs_host(slamgpu *h, const float *z, const int *rows, int K) {
+// One pinned buffer, one copy: [K] float2 z | [K] int row | [K] int row_dst (row_dst == row unless the update kernel
+// re-columns the row on the fly, kernels.cuh K3 REMAP).
+#define OBS_BYTES(cap) ((sizeof(float2) + 2 * sizeof(int)) * (size_t) (cap))
+static int stage_obs_host(slamgpu *h, const float *z, const int *rows, const int *rows_dst, int K, ObsSet *o) {
     if (K > h->obs_cap) {
         int cap = std::max(K, 2 * h->obs_cap);
         CU(cudaStreamSynchronize(h->stream));
         cudaFree(h->d_z); h->d_z = nullptr;
-        cudaFree(h->d_row); h->d_row = nullptr;
         cudaFreeHost(h->h_obs); h->h_obs = nullptr;
-        CU(cudaMalloc(&h->d_z, sizeof(float2) * cap));
-        CU(cudaMalloc(&h->d_row, sizeof(int) * cap));
-        CU(cudaHostAlloc(&h->h_obs, (sizeof(float2) + sizeof(int)) * cap, cudaHostAllocDefault));
+        CU(cudaMalloc(&h->d_z, OBS_BYTES(cap)));
+        CU(cudaHostAlloc(&h->h_obs, OBS_BYTES(cap) * SLAM_OBS_SLOTS, cudaHostAllocDefault));
         h->obs_cap = cap;
     }
-    // the pinned staging block is reused by the next call: wait until the previous copy out of it has been issued
-    // and consumed (stream order makes the kernels safe; the host buffer needs the copy itself to be done)
-    CU(cudaStreamSynchronize(h->stream));
-    float2 *hz = (float2 *) h->h_obs;
-    int *hr = (int *) (hz + h->obs_cap);
+    // pinned staging slots are rotated; a slot is rewritten only after the copy that last read it has run
+    const int slot = h->obs_slot++ % SLAM_OBS_SLOTS;
+    if (!h->obs_ev[slot]) CU(cudaEventCreateWithFlags(&h->obs_ev[slot], cudaEventDisableTiming));
+    else CU(cudaEventSynchronize(h->obs_ev[slot]));
+    float2 *hz = (float2 *) ((char *) h->h_obs + OBS_BYTES(h->obs_cap) * slot);
+    int *hr = (int *) (hz + K);
     for (int i = 0; i < K; i++) {
         hz[i] = make_float2(z[2 * i], z[2 * i + 1]);
         hr[i] = rows[i];
+        hr[K + i] = rows_dst ? rows_dst[i] : rows[i];
     }
-    CU(cudaMemcpyAsync(h->d_z, hz, sizeof(float2) * K, cudaMemcpyHostToDevice, h->stream));
-    CU(cudaMemcpyAsync(h->d_row, hr, sizeof(int) * K, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaMemcpyAsync(h->d_z, hz, OBS_BYTES(K), cudaMemcpyHostToDevice, h->stream));
+    CU(cudaEventRecord(h->obs_ev[slot], h->stream));
+    o->z = h->d_z;
+    o->row = (const int *) (h->d_z + K);
+    o->row_dst = o->row + K;
+    return SLAMGPU_OK;
+}
+
+// Fused re-columning (kernels.cuh K3 REMAP): when every stale observed row belongs to ONE earlier resample epoch (the
+// steady state: the rows observed last step were brought up to date then) the FastSLAM2 update kernel itself reads
+// them through the ancestor map and writes the updated landmarks into fresh physical rows.  Fills src / dst physical
+// rows per observation; *anc == nullptr means "nothing to fuse" (rows are current, or the general path ran).
+static int plan_fused_remap(slamgpu *h, const int *idf, int K, std::vector<int> &src, std::vector<int> &dst,
+                            const int **anc, std::vector<int> &vacated) {
+    *anc = nullptr;
+    long long e = -1;
+    int n_stale = 0;
+    bool one_epoch = true;
+    for (int i = 0; i < K; i++) {
+        const long long re = h->row_epoch[idf[i]];
+        if (re >= h->epoch) continue;
+        if (n_stale && re != e) one_epoch = false;
+        e = re;
+        n_stale++;
+    }
+    if (n_stale == 0) return SLAMGPU_OK;
+    if (h->world > 1 || !one_epoch || (int) h->free_rows.size() < n_stale) {
+        RET(materialise(h, std::vector<int>(idf, idf + K)));  // general path: separate gather kernels
+        for (int i = 0; i < K; i++) src[i] = dst[i] = h->phys_row(idf[i]);
+        return SLAMGPU_OK;
+    }
+    if (h->epoch - e >= h->H) return slam_fail(SLAMGPU_EINVAL, "internal: a landmark row fell out of the resample log");
+    if (e == h->epoch - 1) {
+        *anc = h->keeplog + (size_t) (h->epoch % h->H) * h->Pg + h->slot0;  // one epoch back: keep[] itself
+    } else {
+        TimedSpan sp;
+        RET(span_begin(h, SLAMGPU_T_GATHER, &sp));
+        k_chain<<<grid_for(h->P, 256), 256, 0, h->stream>>>(h->anc, h->P, (long long) h->slot0, (long long) h->Pg,
+                                                            h->keeplog, h->H, h->epoch, e + 1, 1);
+        KCHECK();
+        LAUNCHED(h, SLAMGPU_T_GATHER);
+        RET(span_end(h, &sp));
+        h->stat_chain_steps += h->epoch - e;
+        *anc = h->anc;
+    }
+    for (int i = 0; i < K; i++) {
+        const int l = idf[i];
+        if (h->row_epoch[l] >= h->epoch) continue;
+        dst[i] = h->free_rows.back();
+        h->free_rows.pop_back();
+        vacated.push_back(src[i]);
+        h->phys[l] = dst[i];
+        h->row_epoch[l] = h->epoch;
+    }
+    h->stat_rows_moved += n_stale;
+    h->stat_rows_fused += n_stale;
     return SLAMGPU_OK;
 }
 
@@ -561,25 +647,42 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
     const float4 Rm = make_float4(R[0], R[1], R[2], R[3]);
     const size_t P = h->P;
     if (K > 0) {
-        RET(materialise(h, std::vector<int>(idf, idf + K)));  // observed rows catch up with the resamples since
-        for (int i = 0; i < K; i++) rows[i] = h->phys_row(idf[i]);
-        RET(stage_obs_host(h, zf, rows.data(), K));
+        const bool fast = h->cfg.math_mode == SLAMGPU_MATH_FAST;
+        std::vector<int> dst(K), vacated;
+        const int *anc = nullptr;
+        if (fs2 && fast) {
+            for (int i = 0; i < K; i++) rows[i] = dst[i] = h->phys_row(idf[i]);
+            RET(plan_fused_remap(h, idf, K, rows, dst, &anc, vacated));
+        } else {
+            RET(materialise(h, std::vector<int>(idf, idf + K)));  // observed rows catch up with the resamples since
+            for (int i = 0; i < K; i++) rows[i] = dst[i] = h->phys_row(idf[i]);
+        }
         ObsSet o;
-        o.z = h->d_z;
-        o.row = h->d_row;
+        RET(stage_obs_host(h, zf, rows.data(), dst.data(), K, &o));
         const size_t smem = (sizeof(float2) + sizeof(int)) * K;
         TimedSpan sp;
         RET(span_begin(h, SLAMGPU_T_UPDATE, &sp));
-        const bool fast = h->cfg.math_mode == SLAMGPU_MATH_FAST;
         const size_t smem_fast = SLAM_OBS_OFF_SMEM(K);
         if (fs2 && fast) {
+            const unsigned grid = grid_for(P, SLAM_UPDATE_THREADS), grid_l = std::min<unsigned>(grid, 148u * 4u);
+            const size_t sm_f = SLAM_FS2_FAST_SMEM(K), sm_l = SLAM_OBS_FS2_SMEM(K);
             CU(cudaMemsetAsync(h->fb_count, 0, sizeof(int), h->stream));
-            k_fs2_update_fast<<<grid_for(P, SLAM_UPDATE_THREADS), SLAM_UPDATE_THREADS, SLAM_FS2_FAST_SMEM(K), h->stream>>>(
-                h->soa(h->cur), h->ring(), P, o, K, Rm, dg, h->fb_list, h->fb_count);
-            KCHECK();
-            LAUNCHED(h, SLAMGPU_T_UPDATE);
-            k_fs2_update_listed<<<std::min<unsigned>(grid_for(P, 128), 148u * 4u), 128, smem_fast, h->stream>>>(
-                h->soa(h->cur), h->ring(), P, o, K, Rm, dg, h->fb_list, h->fb_count);
+            if (anc) {
+                k_fs2_update_fast<true><<<grid, SLAM_UPDATE_THREADS, sm_f, h->stream>>>(
+                    h->soa(h->cur), h->ring(), P, o, K, Rm, dg, anc, h->fb_list, h->fb_count);
+                KCHECK();
+                LAUNCHED(h, SLAMGPU_T_UPDATE);
+                k_fs2_update_listed<true><<<grid_l, 128, sm_l, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, dg, anc,
+                                                                            h->fb_list, h->fb_count);
+            } else {
+                k_fs2_update_fast<false><<<grid, SLAM_UPDATE_THREADS, sm_f, h->stream>>>(
+                    h->soa(h->cur), h->ring(), P, o, K, Rm, dg, nullptr, h->fb_list, h->fb_count);
+                KCHECK();
+                LAUNCHED(h, SLAMGPU_T_UPDATE);
+                k_fs2_update_listed<false><<<grid_l, 128, sm_l, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, dg,
+                                                                             nullptr, h->fb_list, h->fb_count);
+            }
+            for (int v : vacated) h->free_rows.insert(h->free_rows.begin(), v);
         } else if (fs2)
             k_fs2_update<<<grid_for(P, 128), 128, smem, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, dg);
         else if (fast)
@@ -595,10 +698,8 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
             rows[i] = h->phys_row(h->Nf + i);
             h->row_epoch[h->Nf + i] = h->epoch;
         }
-        RET(stage_obs_host(h, zn, rows.data(), Kn));
         ObsSet o;
-        o.z = h->d_z;
-        o.row = h->d_row;
+        RET(stage_obs_host(h, zn, rows.data(), nullptr, Kn, &o));
         const size_t smem = (sizeof(float2) + sizeof(int)) * Kn;
         TimedSpan sp;
         RET(span_begin(h, SLAMGPU_T_ADDFEAT, &sp));
@@ -835,13 +936,11 @@ extern "C" int slamgpu_compute_jacobians_batch(slamgpu_t *h, const int32_t *idf,
     }
     RET(materialise(h, std::vector<int>(idf, idf + K)));
     for (int i = 0; i < K; i++) rows[i] = h->phys_row(idf[i]);
-    RET(stage_obs_host(h, z.data(), rows.data(), K));
+    ObsSet o;
+    RET(stage_obs_host(h, z.data(), rows.data(), nullptr, K, &o));
     float4 *dout = nullptr;
     const size_t bytes = sizeof(float) * 16 * (size_t) K * h->P;
     CU(cudaMalloc(&dout, bytes));
-    ObsSet o;
-    o.z = h->d_z;
-    o.row = h->d_row;
     k_jacobians_batch<<<grid_for(h->P, 256), 256, (sizeof(float2) + sizeof(int)) * K, h->stream>>>(
         h->soa(h->cur), h->ring(), h->P, o, K, make_float4(R[0], R[1], R[2], R[3]), dout);
     h->launches++;

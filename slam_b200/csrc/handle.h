@@ -31,6 +31,8 @@ using slam::MapRing;
 using slam::PeerMaps;
 using slam::PoseSoA;
 
+#define SLAM_OBS_SLOTS 4  // rotating pinned staging slots for the observation set
+
 struct Scalars {  // device + pinned mirror
     float ws, s2, csum, neff;
     int anomaly;
@@ -61,7 +63,7 @@ struct slamgpu {
     slam::RowPair *d_pairs = nullptr, *h_pairs = nullptr;  // row-move lists (device / pinned), nf_cap entries
     int *d_phys = nullptr;       // device copy of phys[] for the download helpers
     std::vector<slam::PredictArgs> predict_queue;  // noise-free predict ticks not yet applied (flush_predicts)
-    int64_t stat_rows_moved = 0, stat_resamples = 0, stat_chain_steps = 0;
+    int64_t stat_rows_moved = 0, stat_resamples = 0, stat_chain_steps = 0, stat_rows_fused = 0;
     cudaStream_t stream = nullptr, own_stream = nullptr;
     float *pose[2] = {nullptr, nullptr};  // each: xv[3][P] then Pv[9][P]
     int cur = 0;
@@ -77,8 +79,9 @@ struct slamgpu {
     float *tot_w = nullptr, *tot_c = nullptr, *tot_s = nullptr, *bmax = nullptr;  // [nb_global]
     size_t nb = 0, nbg = 0;      // local / global 1024-blocks
     Scalars *d_sc = nullptr, *h_sc = nullptr;
-    float2 *d_z = nullptr;
-    int *d_row = nullptr;
+    float2 *d_z = nullptr;       // staged observation set: [K] z | [K] row | [K] row_dst (capi.cu stage_obs_host)
+    cudaEvent_t obs_ev[SLAM_OBS_SLOTS] = {nullptr, nullptr, nullptr, nullptr};
+    int obs_slot = 0;
     float *d_rec_in = nullptr, *d_rec_out = nullptr;
     size_t rec_cap = 0;
     int obs_cap = 0;

@@ -63,6 +63,19 @@ struct PredictBatch {
     PredictArgs a[SLAM_PREDICT_QUEUE];
     int n;
 };
+struct PredictBatchFast {  // SLAMGPU_MATH_FAST: control-only terms precomputed on the host (slam_math.cuh PredictTick)
+    PredictTick t[SLAM_PREDICT_QUEUE];
+    int n, with_cov, use_heading;
+};
+__global__ void __launch_bounds__(256) k_predict_batch_fast(PoseSoA s, size_t P, const PredictBatchFast b) {
+    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    const bool need_cov = b.with_cov || b.use_heading;
+    float x[3], C[9];
+    load_pose(s, P, p, x, need_cov ? C : nullptr);
+    for (int t = 0; t < b.n; t++) predict_tick_fast(x, C, b.t[t], b.with_cov != 0, b.use_heading != 0);
+    store_pose(s, P, p, x, need_cov ? C : nullptr);
+}
 __global__ void __launch_bounds__(256) k_predict_batch(PoseSoA s, size_t P, const PredictBatch b) {
     const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= P) return;
@@ -87,6 +100,8 @@ __global__ void __launch_bounds__(256) k_predict_batch(PoseSoA s, size_t P, cons
 struct ObsSet {           // device arrays written by the host before the launch
     const float2 *z;      // [K] range, bearing
     const int *row;       // [K] PHYSICAL landmark row
+    const int *row_dst;   // [K] fused re-columning (K3 REMAP): the physical row the updated landmark is written to;
+                          //     row_dst[i] != row[i] marks a row whose columns still belong to the previous resample
 };
 
 __device__ __forceinline__ void lm_load(const MapRing &m, size_t P, int row, size_t p, float *xf, float *Pf) {
@@ -179,8 +194,10 @@ __device__ __forceinline__ void lm_load_at(const float2 *mp, const float4 *cp, f
 // is NOT processed by the fast kernel: its index goes to a list and k_fs2_update_listed, launched right behind,
 // gives it the reference-order routine (so Eigen's behaviour on a failed LLT is still reproduced).  Keeping that
 // routine out of the fast kernel keeps its ~80 registers out of the fast kernel's allocation.
+template <bool REMAP>
 __device__ __forceinline__ void fs2_update_particle_reference_order(PoseSoA s, MapRing m, size_t P, size_t p,
                                                                     const float2 *sz, const unsigned long long *soff,
+                                                                    const unsigned long long *doff, long long q,
                                                                     int K, float4 Rm, const float *gauss) {
     const float R[4] = {Rm.x, Rm.y, Rm.z, Rm.w};
     float x[3], C[9], x0[3], C0[9];
@@ -190,7 +207,8 @@ __device__ __forceinline__ void fs2_update_particle_reference_order(PoseSoA s, M
     const float g3[3] = {gauss[p], gauss[P + p], gauss[2 * P + p]};
     float xf[2], Pf[4];
     for (int i = 0; i < K; i++) {
-        lm_load_at(m.mean + soff[i] + p, m.cov + soff[i] + p, xf, Pf);
+        const size_t src = soff[i] + ((REMAP && soff[i] != doff[i]) ? (size_t) q : p);
+        lm_load_at(m.mean + src, m.cov + src, xf, Pf);
         const float z[2] = {sz[i].x, sz[i].y};
         proposal_step(x, C, R, xf, Pf, z);
     }
@@ -202,11 +220,13 @@ __device__ __forceinline__ void fs2_update_particle_reference_order(PoseSoA s, M
     const float prop = gauss_evaluate<3>(v2, C);
     float like = 1.0f;
     for (int i = 0; i < K; i++) {
-        lm_load_at(m.mean + soff[i] + p, m.cov + soff[i] + p, xf, Pf);
+        const size_t src = soff[i] + ((REMAP && soff[i] != doff[i]) ? (size_t) q : p);
+        const size_t dst = (REMAP ? doff[i] : soff[i]) + p;
+        lm_load_at(m.mean + src, m.cov + src, xf, Pf);
         const float z[2] = {sz[i].x, sz[i].y};
         like = like * likelihood_and_feature_update(xs, R, xf, Pf, z);
-        __stcs(m.mean + soff[i] + p, make_float2(xf[0], xf[1]));
-        __stcs(m.cov + soff[i] + p, make_float4(Pf[0], Pf[2], Pf[1], Pf[3]));
+        __stcs(m.mean + dst, make_float2(xf[0], xf[1]));
+        __stcs(m.cov + dst, make_float4(Pf[0], Pf[2], Pf[1], Pf[3]));
     }
     s.w[p] = s.w[p] * like * prior / prop;
     const float Z[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
@@ -227,15 +247,43 @@ __device__ __forceinline__ void stage_obs_off(const ObsSet &o, int K, size_t P, 
 }
 #define SLAM_OBS_OFF_SMEM(K) ((sizeof(unsigned long long) + sizeof(float2)) * ((K) + 1))
 
+// Shared-memory staging of the FastSLAM2 fast kernels: source / destination element offsets (row * P) and z.
+template <bool REMAP>
+__device__ __forceinline__ void stage_obs_fs2(unsigned char *base, const ObsSet &o, int K, size_t P, float2 *&sz,
+                                              unsigned long long *&soff, unsigned long long *&doff) {
+    soff = reinterpret_cast<unsigned long long *>(base);
+    doff = soff + K;
+    sz = reinterpret_cast<float2 *>(doff + K);
+    for (int i = threadIdx.x; i < K; i += blockDim.x) {
+        sz[i] = o.z[i];
+        soff[i] = (unsigned long long) o.row[i] * (unsigned long long) P;
+        doff[i] = (unsigned long long) (REMAP ? o.row_dst[i] : o.row[i]) * (unsigned long long) P;
+    }
+    __syncthreads();
+}
+#define SLAM_OBS_FS2_SMEM(K) ((2 * sizeof(unsigned long long) + sizeof(float2)) * (K))
+
+// anc: the resample's keep[] (or a composed ancestor map) for this device's slots; -1 means "the last particle"
+// exactly as in k_gather_pose (core.cpp:800-806 leaves -1 where select ran past the CDF).
+__device__ __forceinline__ long long remap_column(const int *__restrict__ anc, size_t p, size_t P) {
+    const int k = anc[p];
+    return k < 0 ? (long long) P - 1 : (long long) k;
+}
+
+template <bool REMAP>
 __global__ void __launch_bounds__(128) k_fs2_update_listed(PoseSoA s, MapRing m, size_t P, ObsSet o, int K, float4 Rm,
                                                            const float *__restrict__ gauss,
+                                                           const int *__restrict__ anc,
                                                            const int *__restrict__ list, const int *__restrict__ count) {
     float2 *sz;
-    unsigned long long *soff;
-    stage_obs_off(o, K, P, sz, soff);
+    unsigned long long *soff, *doff;
+    stage_obs_fs2<REMAP>(slam_smem, o, K, P, sz, soff, doff);
     const int n = *count;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-        fs2_update_particle_reference_order(s, m, P, (size_t) list[i], sz, soff, K, Rm, gauss);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const size_t p = (size_t) list[i];
+        fs2_update_particle_reference_order<REMAP>(s, m, P, p, sz, soff, doff, REMAP ? remap_column(anc, p, P) : 0, K,
+                                                   Rm, gauss);
+    }
 }
 
 // Per-thread asynchronous landmark ring.  Each thread copies ITS OWN column of the next landmark rows from HBM into its
@@ -260,32 +308,36 @@ __device__ __forceinline__ void cp_async_wait() {
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 #define SLAM_FS2_FAST_SMEM(K) \
-    ((sizeof(float4) + sizeof(float2)) * SLAM_RING_DEPTH * SLAM_UPDATE_THREADS + SLAM_OBS_OFF_SMEM(K))
+    ((sizeof(float4) + sizeof(float2)) * SLAM_RING_DEPTH * SLAM_UPDATE_THREADS + SLAM_OBS_FS2_SMEM(K))
 
+// REMAP = the re-columning of deferred map resampling (K7) fused into the update: an observed row whose columns still
+// belong to the previous resample epoch is READ at column anc[p] of its old physical row and the updated landmark is
+// WRITTEN to column p of a fresh physical row, so the row needs no separate k_materialise_rows pass (one read + one
+// write of 24 B per particle-landmark saved on every update that follows a resample).
+template <bool REMAP>
 __global__ void __launch_bounds__(SLAM_UPDATE_THREADS) k_fs2_update_fast(PoseSoA s, MapRing m, size_t P, ObsSet o, int K,
                                                                          float4 Rm, const float *__restrict__ gauss,
+                                                                         const int *__restrict__ anc,
                                                                          int *__restrict__ list, int *__restrict__ count) {
     constexpr int D = SLAM_RING_DEPTH, T = SLAM_UPDATE_THREADS;
     float4 *const ring_cov = reinterpret_cast<float4 *>(slam_smem) + threadIdx.x;                // slot s at [s * T]
     float2 *const ring_mean = reinterpret_cast<float2 *>(reinterpret_cast<float4 *>(slam_smem) + D * T) + threadIdx.x;
-    unsigned long long *const soff = reinterpret_cast<unsigned long long *>(
-        slam_smem + (sizeof(float4) + sizeof(float2)) * D * T);
-    float2 *const sz = reinterpret_cast<float2 *>(soff + (K + 1));
-    for (int i = threadIdx.x; i < K; i += blockDim.x) {
-        sz[i] = o.z[i];
-        soff[i] = (unsigned long long) o.row[i] * (unsigned long long) P;
-    }
-    __syncthreads();
+    float2 *sz;
+    unsigned long long *soff, *doff;
+    stage_obs_fs2<REMAP>(slam_smem + (sizeof(float4) + sizeof(float2)) * D * T, o, K, P, sz, soff, doff);
     const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= P) return;
     const float2 *const mean_p = m.mean + p;
     const float4 *const cov_p = m.cov + p;
+    const long long dq = REMAP ? remap_column(anc, p, P) - (long long) p : 0;  // column shift of a stale row's source
+#define SLAM_SRC_OFF(i) (REMAP ? (long long) soff[i] + ((soff[i] != doff[i]) ? dq : 0ll) : (long long) soff[i])
     // the first D-1 rows go in flight before anything else is looked at
 #pragma unroll
     for (int j = 0; j < D - 1; j++) {
         if (j < K) {
-            cp_async_8(ring_mean + j * T, mean_p + soff[j]);
-            cp_async_16(ring_cov + j * T, cov_p + soff[j]);
+            const long long off = SLAM_SRC_OFF(j);
+            cp_async_8(ring_mean + j * T, mean_p + off);
+            cp_async_16(ring_cov + j * T, cov_p + off);
         }
         cp_async_commit();
     }
@@ -310,7 +362,7 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS) k_fs2_update_fast(PoseSoA
             if (i < K) {
                 const int j = i + D - 1;
                 if (j < K) {
-                    const unsigned long long noff = soff[j];
+                    const long long noff = SLAM_SRC_OFF(j);
                     cp_async_8(ring_mean + ((sl + D - 1) % D) * T, mean_p + noff);
                     cp_async_16(ring_cov + ((sl + D - 1) % D) * T, cov_p + noff);
                 }
@@ -337,9 +389,9 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS) k_fs2_update_fast(PoseSoA
             if (i < K) {
                 cp_async_wait<D - 1>();
                 lm_load_at(ring_mean + sl * T, ring_cov + sl * T, xf, Pf);
-                const unsigned long long off = soff[i];
+                const unsigned long long off = doff[i];
                 if (i - D >= 0) {  // the slot just read takes row i - D
-                    const unsigned long long noff = soff[i - D];
+                    const long long noff = SLAM_SRC_OFF(i - D);
                     cp_async_8(ring_mean + sl * T, mean_p + noff);
                     cp_async_16(ring_cov + sl * T, cov_p + noff);
                 }
@@ -354,6 +406,7 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS) k_fs2_update_fast(PoseSoA
     s.w[p] = s.w[p] * like * ratio;
     const float Z[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
     store_pose(s, P, p, xs, Z);
+#undef SLAM_SRC_OFF
 }
 
 __global__ void __launch_bounds__(256) k_fs1_update_fast(PoseSoA s, MapRing m, size_t P, ObsSet o, int K, float4 Rm) {

@@ -545,6 +545,90 @@ SLAM_HD void chol3_inverse(const float *L, float *c) {
     c[5] = m22 * m22;
 }
 
+// ---- predict, fast formulation -------------------------------------------------------------------------------------
+// One noise-free FastSLAM2::predict tick (fastslam2.cpp:51-60,70-125) with the structure of its matrices used instead
+// of dense 3x3 products: Gv = I + [0 0 a; 0 0 b; 0 0 0], and josephUpdate's C = I - W*[0 0 1] (core.cpp:294-317), so
+// Gv*Pv*Gv' and C*Pv*C' are two rank-one row/column updates each.  Skipping the exact zeros and ones of the dense
+// products changes no rounding by itself; what differs from the reference-order path is FMA contraction, sincosf
+// for the pair (sin, cos)(G + phi), the reciprocal and the single-rounding angle wrap.  Everything that depends only
+// on the controls (sin(G/wb): note the reference's G/wheelBase INSIDE the sine, fastslam2.cpp:103; sin G, cos G in
+// Gu) is evaluated once on the host (PredictTick).  Pv stays a general (not symmetrised) 3x3, like the reference's.
+// ~120 instructions per tick instead of ~430 (ncu r01: k_predict_batch was fp32-issue bound at 122 us for 8 ticks).
+struct PredictTick {
+    float vdt;      // V*dt
+    float dt;
+    float dtheta;   // V*dt*sin(G/wheelBase)
+    float G;
+    float gu20, gu21;  // third row of Gu: dt*sin(G)/wb, V*dt*cos(G)/wb
+    float Q[4];
+    float phi_true, R_phi;  // heading observation and its variance sigmaT^2
+};
+
+SLAM_HD void predict_tick_fast(float *x, float *C, const PredictTick &t, bool with_cov, bool use_heading) {
+    float s, c;
+#if defined(__CUDA_ARCH__)
+    sincosf(t.G + x[2], &s, &c);
+#else
+    s = sinf(t.G + x[2]);
+    c = cosf(t.G + x[2]);
+#endif
+    const float a = -t.vdt * s, b = t.vdt * c;
+    if (with_cov) {
+        // T1 = Gv*C: rows 0 and 1 pick up a, b times row 2;  T2 = T1*Gv': columns 0 and 1 pick up a, b times column 2
+        float T[9];
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            T[j] = fmaf(a, C[6 + j], C[j]);
+            T[3 + j] = fmaf(b, C[6 + j], C[3 + j]);
+            T[6 + j] = C[6 + j];
+        }
+#pragma unroll
+        for (int i = 0; i < 3; i++) {
+            T[i * 3 + 0] = fmaf(a, T[i * 3 + 2], T[i * 3 + 0]);
+            T[i * 3 + 1] = fmaf(b, T[i * 3 + 2], T[i * 3 + 1]);
+        }
+        // Gu*Q*Gu', Gu = [dt*c a; dt*s b; gu20 gu21]
+        const float Gu[6] = {t.dt * c, a, t.dt * s, b, t.gu20, t.gu21};
+        float M[6];
+#pragma unroll
+        for (int i = 0; i < 3; i++) {
+            M[i * 2 + 0] = fmaf(Gu[i * 2], t.Q[0], Gu[i * 2 + 1] * t.Q[2]);
+            M[i * 2 + 1] = fmaf(Gu[i * 2], t.Q[1], Gu[i * 2 + 1] * t.Q[3]);
+        }
+#pragma unroll
+        for (int i = 0; i < 3; i++)
+#pragma unroll
+            for (int j = 0; j < 3; j++)
+                C[i * 3 + j] = fmaf(M[i * 2], Gu[j * 2], fmaf(M[i * 2 + 1], Gu[j * 2 + 1], T[i * 3 + j]));
+    }
+    x[0] += b;   // x + V*dt*cos(G + phi)
+    x[1] -= a;   // y + V*dt*sin(G + phi)
+    x[2] = wrap_fast(x[2] + t.dtheta);
+    if (use_heading) {
+        const float v = wrap_fast(t.phi_true - x[2]);
+        const float Si = SLAM_RCP(C[8] + t.R_phi);
+        const float W[3] = {C[2] * Si, C[5] * Si, C[8] * Si};
+        x[0] = fmaf(W[0], v, x[0]);
+        x[1] = fmaf(W[1], v, x[1]);
+        x[2] = fmaf(W[2], v, x[2]);
+        // CP = C - W * C[2,:];  CPC = CP - CP[:,2] * W';  + W*R*W' + eps*I
+        float CP[9];
+#pragma unroll
+        for (int i = 0; i < 3; i++)
+#pragma unroll
+            for (int j = 0; j < 3; j++) CP[i * 3 + j] = fmaf(-W[i], C[6 + j], C[i * 3 + j]);
+#pragma unroll
+        for (int i = 0; i < 3; i++) {
+            const float wr = W[i] * t.R_phi;
+#pragma unroll
+            for (int j = 0; j < 3; j++) {
+                const float v2 = fmaf(wr, W[j], fmaf(-CP[i * 3 + 2], W[j], CP[i * 3 + j]));
+                C[i * 3 + j] = (i == j) ? v2 + 2.2204e-16f : v2;
+            }
+        }
+    }
+}
+
 // Pose-side state of the information-form proposal.
 struct ProposalInfo {
     float lam[6];  // Lambda = Pv^-1, packed lower (00, 10, 11, 20, 21, 22)

@@ -50,6 +50,30 @@ void he_predict(int method, long P, float *xv, float *Pv, float V, float G, cons
     }
 }
 
+// what capi.cu:flush_predicts + k_predict_batch_fast do for one noise-free tick
+void he_predict_fast(int method, long P, float *xv, float *Pv, float V, float G, const float *Q, float dt,
+                     float phi_true, float wheel_base, float sigma_phi, int use_heading) {
+    PredictTick k;
+    k.vdt = V * dt;
+    k.dt = dt;
+    k.dtheta = V * dt * sinf(G / wheel_base);
+    k.G = G;
+    k.gu20 = dt * sinf(G) / wheel_base;
+    k.gu21 = V * dt * cosf(G) / wheel_base;
+    for (int j = 0; j < 4; j++) k.Q[j] = Q[j];
+    k.phi_true = phi_true;
+    k.R_phi = sigma_phi * sigma_phi;
+    for (long p = 0; p < P; p++) {
+        float x[3], C[9];
+        for (int c = 0; c < 3; c++) x[c] = xv[c * P + p];
+        for (int j = 0; j < 9; j++) C[j] = Pv[j * P + p];
+        predict_tick_fast(x, C, k, method == 2, use_heading != 0);
+        for (int c = 0; c < 3; c++) xv[c * P + p] = x[c];
+        if (method == 2 || use_heading)
+            for (int j = 0; j < 9; j++) Pv[j * P + p] = C[j];
+    }
+}
+
 int he_fs2_update_particles(long P, int Nf, float *xv, float *Pv, float *w, float *lm_mean, float *lm_cov,
                             const float *zf, const int *idf, int K, const float *zn, int Kn, const float *R,
                             const float *gauss) {

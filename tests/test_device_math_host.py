@@ -37,6 +37,11 @@ def emul():
     L.he_fs1_update_particles.restype = C.c_int
     L.he_fs1_update_particles.argtypes = [C.c_long, C.c_int, f32p, f32p, f32p, f32p, f32p, f32p, i32p, C.c_int, f32p,
                                           C.c_int, f32p]
+    L.he_predict_fast.argtypes = [C.c_int, C.c_long, f32p, f32p, C.c_float, C.c_float, f32p, C.c_float, C.c_float,
+                                  C.c_float, C.c_float, C.c_int]
+    L.he_fs2_update_particles_fast.restype = C.c_int
+    L.he_fs2_update_particles_fast.argtypes = [C.c_long, C.c_int, f32p, f32p, f32p, f32p, f32p, f32p, i32p, C.c_int,
+                                               f32p, f32p]
     return L
 
 
@@ -117,3 +122,44 @@ def test_synthetic_cfg4_shape_update(emul, oracle):
     wa, wb = a.w / a.w.sum(), b.w / b.w.sum()
     errs = compare_states(snapshot(b), snapshot(a), 1e-4, "cfg4-shape update", tol_w=1e9)
     assert np.abs(wa - wb).max() <= 1e-4 * wa.max(), errs
+
+
+@pytest.mark.parametrize("method,heading", [(2, True), (2, False), (1, True)])
+def test_fast_predict_ticks_match_oracle(emul, oracle, method, heading):
+    """SLAMGPU_MATH_FAST predict (predict_tick_fast: sparse Gv / Joseph forms, host-side control terms) against the
+    oracle's dense reference-order predict over 5 cycles of 8 noise-free ticks, steering through both signs."""
+    from oracle.pyoracle import State
+    P = 128
+    rng = np.random.default_rng(21)
+    a, b = State(P, 1), State(P, 1)
+    a.xv[:] = rng.normal(0, 1, (3, P)).astype(np.float32)
+    a.xv[2] = rng.uniform(-3.1, 3.1, P).astype(np.float32)
+    b.xv[:] = a.xv
+    Q = _f(Q_DEFAULT).ravel()
+    phi = 0.3
+    for tick in range(40):
+        V, G = 3.0 + 0.1 * tick, 0.5 * np.sin(0.3 * tick)
+        phi = float(np.float32(phi + V * DT * np.sin(G) / WHEELBASE))
+        oracle.predict(method, a, V, G, Q_DEFAULT, DT, phi, WHEELBASE, SIGMA_PHI, heading, None)
+        emul.he_predict_fast(method, P, b.xv, b.Pv, V, G, Q, DT, phi, WHEELBASE, SIGMA_PHI, int(heading))
+        compare_states(snapshot(b), snapshot(a), 1e-4, "fast predict tick %d" % tick, tol_w=1e-4)
+
+
+def test_fast_fs2_update_matches_oracle(emul, oracle):
+    """SLAMGPU_MATH_FAST FastSLAM2 update (information-form proposal, shared factors, symmetric-part S) on the cfg-4
+    style synthetic state against the oracle."""
+    from oracle.pyoracle import State
+    P, Nf, K = 256, 64, 32
+    d = synthetic_state(P, Nf, K, seed=5)
+    rng = np.random.default_rng(10)
+    gauss = rng.standard_normal((3, P)).astype(np.float32)
+    a, b = State(P, Nf), State(P, Nf)
+    for s_ in (a, b):
+        s_.xv[:], s_.Pv[:], s_.w[:], s_.lm_mean[:], s_.lm_cov[:] = d["xv"], d["Pv"], d["w"], d["lm_mean"], d["lm_cov"]
+        s_.Nf = Nf
+    oracle.update_particles(2, a, d["zf"], d["idf"], np.zeros((0, 2), np.float32), d["R"], gauss)
+    emul.he_fs2_update_particles_fast(P, Nf, b.xv, b.Pv, b.w, b.lm_mean, b.lm_cov, _f(d["zf"]),
+                                      np.ascontiguousarray(d["idf"], np.int32), K, _f(d["R"]).ravel(), gauss)
+    wa, wb = a.w / a.w.sum(), b.w / b.w.sum()
+    errs = compare_states(snapshot(b), snapshot(a), 1e-4, "fast cfg4-shape update", tol_w=1e9)
+    assert np.abs(wa - wb).max() <= 2e-4 * wa.max(), errs

@@ -244,6 +244,64 @@ def test_resample_moves_whole_map_deferred(sb, oracle, log_epochs, spare):
         assert st["rows_moved"] < 13 * Nf
 
 
+@pytest.mark.parametrize("P,pv_zero", [(5000, False), (1000, True)])
+def test_update_recolumns_observed_rows_in_kernel(sb, oracle, P, pv_zero):
+    """Deferred map resampling fused into the FastSLAM2 update (kernels.cuh K3 REMAP): after a forced resample the
+    observed rows are stale by exactly one epoch, so the update kernel reads them through keep[] and writes fresh
+    rows itself.  Handle A has spare rows (fused path); handle B has a single spare row, which forces the separate
+    k_chain / k_materialise_rows gather that the other tests pin against the oracle's eager copy.  Both receive the
+    same calls; the map is never downloaded in between (a download would bring every row up to date).  A copy
+    commutes with being fused: poses, weights, keep[] and every landmark row must agree BIT FOR BIT after 4 cycles.
+    The first cycle is also held against the oracle (later cycles of this repeated-observation scenario amplify
+    rounding differences between any two fp32 orders, the reference-order kernel included, beyond the 1e-4 bar).
+    pv_zero leaves Pv at zero after the first pose sample (no predict in between), which sends every particle of cycle
+    1 through the listed reference-order kernel - the same remap there; like Eigen's LLT on a zero matrix that path
+    yields NaN poses (the reference's behaviour), so equality is NaN-aware and only cycle 1 exercises the remap."""
+    from gpu_util import gpu_snapshot, make_backend, upload_state
+    from oracle.pyoracle import State
+    from slam_b200.synthetic import SyntheticDrive
+    Nf, K = 40, 12
+    d = synthetic_state(P, Nf, K, seed=8, extent=40.0)
+    rng = np.random.default_rng(13)
+    s = State(P, Nf)
+    s.xv[:], s.Pv[:], s.w[:], s.lm_mean[:], s.lm_cov[:] = d["xv"], d["Pv"], d["w"], d["lm_mean"], d["lm_cov"]
+    s.Nf = Nf
+    fa = make_backend(2, P, Nf, n_effective=P + 1, scan_mode=sb.SCAN_BLOCKED)
+    fb = make_backend(2, P, Nf, n_effective=P + 1, scan_mode=sb.SCAN_BLOCKED, spare_rows=1)
+    upload_state(fa, s)
+    upload_state(fb, s)
+    drive = SyntheticDrive(d["lm"], K, d["R"])
+    for cycle in range(4):
+        if not pv_zero or cycle == 0:
+            for _ in range(2):
+                V, G, dt, phi = drive.controls()
+                fa.predict(V, G, Q_DEFAULT, dt, phi)
+                fb.predict(V, G, Q_DEFAULT, dt, phi)
+                if cycle == 0:
+                    oracle.predict(2, s, V, G, Q_DEFAULT, dt, phi, WHEELBASE, SIGMA_PHI, True, None)
+        zf, idf = drive.observe()
+        gauss = rng.standard_normal((3, P)).astype(np.float32)
+        unif = rng.random(P)
+        fa.update_particles(zf, idf, np.zeros((0, 2), np.float32), d["R"], gauss)
+        fb.update_particles(zf, idf, np.zeros((0, 2), np.float32), d["R"], gauss)
+        ga, gb = fa.download(landmarks=False), fb.download(landmarks=False)  # poses and weights: the map stays deferred
+        for k in ("xv", "Pv", "w"):
+            assert np.array_equal(ga[k], gb[k], equal_nan=True), (cycle, k)
+        if cycle == 0:
+            oracle.update_particles(2, s, zf, idf, np.zeros((0, 2), np.float32), d["R"], gauss)
+            wa, wb = ga["w"] / ga["w"].sum(), s.w / s.w.sum()
+            assert np.abs(wa - wb).max() <= 2e-3 * wb.max()
+        ka, neff_a, did_a = fa.resample(unif, want_keep=True)
+        kb, neff_b, did_b = fb.resample(unif, want_keep=True)
+        assert did_a == did_b and np.array_equal(ka, kb), cycle
+        assert (did_a and neff_a == neff_b) or (pv_zero and cycle > 0), cycle
+    assert fa.stats()["rows_fused"] >= (1 if pv_zero else 3) * (K - 1) and fb.stats()["rows_fused"] == 0
+    ga, gb = gpu_snapshot(fa), gpu_snapshot(fb)
+    for k in ("xv", "Pv", "w", "lm_mean", "lm_cov"):
+        assert np.array_equal(ga[k], gb[k], equal_nan=True), k
+    assert pv_zero or np.isfinite(ga["lm_mean"]).all()
+
+
 def test_error_paths(sb):
     from gpu_util import make_backend
     f = make_backend(2, 128, 2)
