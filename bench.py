@@ -239,7 +239,7 @@ def run_ours(a):
     P, Nf, K = a.particles, a.landmarks, a.obs
     Pg = P * world
     tile = min(a.tile, P)
-    d = synthetic_state(tile, Nf, K, seed=1 + rank)
+    d = synthetic_state(tile, Nf, K, seed=1 + rank, map_seed=1)  # one world, different particles per rank
     f = slam_b200.FastSLAM(slam_b200.FASTSLAM2, P, Nf, wheel_base=WHEELBASE, sigma_phi=SIGMA_PHI,
                            n_effective=int(0.75 * Pg), use_heading=True, scan_mode=slam_b200.SCAN_BLOCKED,
                            device=local)

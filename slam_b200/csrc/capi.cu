@@ -306,6 +306,8 @@ static int peer_maps(slamgpu *h, PeerMaps *pm) {
     pm->pose[1][0] = h->pose[1];
     pm->mean[0] = h->lm_mean;
     pm->cov[0] = h->lm_cov;
+    pm->cdf[0] = h->cdf;
+    pm->mloc[0] = h->mloc;
     return SLAMGPU_OK;
 }
 
@@ -572,22 +574,35 @@ static int stage_obs_host(slamgpu *h, const float *z, const int *rows, const int
 static int plan_fused_remap(slamgpu *h, const int *idf, int K, std::vector<int> &src, std::vector<int> &dst,
                             const int **anc, std::vector<int> &vacated) {
     *anc = nullptr;
+    // the epoch most stale observed rows share is fused; rows of any other epoch (newcomers to the observed set)
+    // catch up first through the separate gather kernels
+    std::vector<long long> eps;
+    for (int i = 0; i < K; i++)
+        if (h->row_epoch[idf[i]] < h->epoch) eps.push_back(h->row_epoch[idf[i]]);
     long long e = -1;
     int n_stale = 0;
-    bool one_epoch = true;
-    for (int i = 0; i < K; i++) {
-        const long long re = h->row_epoch[idf[i]];
-        if (re >= h->epoch) continue;
-        if (n_stale && re != e) one_epoch = false;
-        e = re;
-        n_stale++;
+    if (!eps.empty()) {
+        std::sort(eps.begin(), eps.end());
+        for (size_t i = 0; i < eps.size();) {
+            size_t j = i;
+            while (j < eps.size() && eps[j] == eps[i]) j++;
+            if ((int) (j - i) >= n_stale) {  // ties: the newer epoch (shorter ancestor chain)
+                n_stale = (int) (j - i);
+                e = eps[i];
+            }
+            i = j;
+        }
+        std::vector<int> others;
+        const bool fuse = (int) h->free_rows.size() >= n_stale;
+        for (int i = 0; i < K; i++) {
+            const long long re = h->row_epoch[idf[i]];
+            if (re < h->epoch && (!fuse || re != e)) others.push_back(idf[i]);
+        }
+        if (!others.empty()) RET(materialise(h, others));
+        if (!fuse) n_stale = 0;
     }
+    for (int i = 0; i < K; i++) src[i] = dst[i] = h->phys_row(idf[i]);
     if (n_stale == 0) return SLAMGPU_OK;
-    if (h->world > 1 || !one_epoch || (int) h->free_rows.size() < n_stale) {
-        RET(materialise(h, std::vector<int>(idf, idf + K)));  // general path: separate gather kernels
-        for (int i = 0; i < K; i++) src[i] = dst[i] = h->phys_row(idf[i]);
-        return SLAMGPU_OK;
-    }
     if (h->epoch - e >= h->H) return slam_fail(SLAMGPU_EINVAL, "internal: a landmark row fell out of the resample log");
     if (e == h->epoch - 1) {
         *anc = h->keeplog + (size_t) (h->epoch % h->H) * h->Pg + h->slot0;  // one epoch back: keep[] itself
@@ -667,20 +682,39 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
             const unsigned grid = grid_for(P, SLAM_UPDATE_THREADS), grid_l = std::min<unsigned>(grid, 148u * 4u);
             const size_t sm_f = SLAM_FS2_FAST_SMEM(K), sm_l = SLAM_OBS_FS2_SMEM(K);
             CU(cudaMemsetAsync(h->fb_count, 0, sizeof(int), h->stream));
+            PeerRows pr;
+            memset(&pr, 0, sizeof(pr));
+            pr.world = 1;
+            pr.mean[0] = h->lm_mean;
+            pr.cov[0] = h->lm_cov;
+            if (anc && h->world > 1) {
+                // stale rows are read from the rank that holds the ancestor: every rank's earlier writes must have
+                // landed, and the fresh rows written here must no longer be read by anyone (they were vacated by an
+                // earlier kernel of some rank): one stream-ordered barrier covers both
+                PeerMaps pm;
+                RET(peer_maps(h, &pm));
+                for (int r = 0; r < h->world; r++) {
+                    pr.mean[r] = pm.mean[r];
+                    pr.cov[r] = pm.cov[r];
+                }
+                pr.world = h->world;
+                RET(comm_barrier(h->comm, h->stream));
+            }
+            const long long Pgl = (long long) h->Pg;
             if (anc) {
                 k_fs2_update_fast<true><<<grid, SLAM_UPDATE_THREADS, sm_f, h->stream>>>(
-                    h->soa(h->cur), h->ring(), P, o, K, Rm, dg, anc, h->fb_list, h->fb_count);
+                    h->soa(h->cur), h->ring(), P, o, K, Rm, dg, anc, pr, Pgl, h->fb_list, h->fb_count);
                 KCHECK();
                 LAUNCHED(h, SLAMGPU_T_UPDATE);
                 k_fs2_update_listed<true><<<grid_l, 128, sm_l, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, dg, anc,
-                                                                            h->fb_list, h->fb_count);
+                                                                            pr, Pgl, h->fb_list, h->fb_count);
             } else {
                 k_fs2_update_fast<false><<<grid, SLAM_UPDATE_THREADS, sm_f, h->stream>>>(
-                    h->soa(h->cur), h->ring(), P, o, K, Rm, dg, nullptr, h->fb_list, h->fb_count);
+                    h->soa(h->cur), h->ring(), P, o, K, Rm, dg, nullptr, pr, Pgl, h->fb_list, h->fb_count);
                 KCHECK();
                 LAUNCHED(h, SLAMGPU_T_UPDATE);
                 k_fs2_update_listed<false><<<grid_l, 128, sm_l, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, dg,
-                                                                             nullptr, h->fb_list, h->fb_count);
+                                                                             nullptr, pr, Pgl, h->fb_list, h->fb_count);
             }
             for (int v : vacated) h->free_rows.insert(h->free_rows.begin(), v);
         } else if (fs2)
@@ -759,8 +793,10 @@ static int resample_indices(slamgpu *h) {
     KCHECK();
     LAUNCHED(h, SLAMGPU_T_WEIGHTS);
     if (h->world > 1) {
+        RET(comm_group_begin(h->comm));
         RET(comm_allgather_f32(h->comm, h->tot_c, h->nb, h->stream));
         RET(comm_allgather_f32(h->comm, h->tot_s, h->nb, h->stream));
+        RET(comm_group_end(h->comm));
     }
     // D: recursive levels of both -> csum, s2
     RET(launch_upper(h, h->tot_c, &d->csum, h->tot_s, &d->s2, (int) h->nbg, 0));
@@ -772,19 +808,28 @@ static int resample_indices(slamgpu *h) {
                                                           h->bmax + b0);
     KCHECK();
     LAUNCHED(h, SLAMGPU_T_WEIGHTS);
+    PeerMaps pm;
+    RET(peer_maps(h, &pm));
     if (h->world > 1) {
+        // the block maxima are exchanged; the CDF and its running maxima stay where they are and are read through the
+        // peer mappings.  This exchange is also the stream-ordered barrier that makes every rank's k_cdf_finalise
+        // visible before any rank searches (and the next update's first exchange keeps a rank from overwriting its
+        // CDF while a peer still searches it).
+        RET(comm_group_begin(h->comm));
         RET(comm_allgather_f32(h->comm, h->bmax, h->nb, h->stream));
-        RET(comm_allgather_f32(h->comm, h->cdf, P, h->stream));
-        RET(comm_allgather_f32(h->comm, h->mloc, P, h->stream));
         RET(comm_halo_unif(h->comm, h->unif_base, P, h->stream));
+        RET(comm_group_end(h->comm));
     }
     RET(launch_upper(h, h->bmax, nullptr, nullptr, nullptr, (int) h->nbg, 1));
     // F: select + search
     SearchArgs a;
     a.di = h->di();
     a.unif = h->unif();
-    a.cdf = h->cdf;
-    a.mloc = h->mloc;
+    for (int r = 0; r < SLAM_MAX_RANKS; r++) {
+        a.cdf[r] = pm.cdf[r];
+        a.mloc[r] = pm.mloc[r];
+    }
+    a.world = h->world;
     a.BM = h->bmax;
     a.sel = h->sel;
     a.keep = h->keep;

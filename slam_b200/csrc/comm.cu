@@ -56,7 +56,7 @@ struct SlamComm {
     ncclComm_t comm = nullptr;
     bool peers_open = false;
     PeerMaps peers;
-    void *opened[SLAM_MAX_RANKS][4];
+    void *opened[SLAM_MAX_RANKS][6];
     unsigned char *d_small = nullptr;  // scratch for handle exchange, barriers, estimate
     unsigned char *h_small = nullptr;
 };
@@ -113,7 +113,7 @@ SlamComm *comm_create(int rank, int world, const void *id128, int device, std::s
 void comm_destroy(SlamComm *c) {
     if (!c) return;
     for (int r = 0; r < c->world; r++)
-        for (int j = 0; j < 4; j++)
+        for (int j = 0; j < 6; j++)
             if (c->opened[r][j]) cudaIpcCloseMemHandle(c->opened[r][j]);
     if (c->comm) g_nccl.CommDestroy(c->comm);
     if (c->d_small) cudaFree(c->d_small);
@@ -143,23 +143,23 @@ static int barrier(SlamComm *c, cudaStream_t st) {
 
 static int open_peers(SlamComm *c, slamgpu *h) {
     if (c->peers_open) return SLAMGPU_OK;
-    cudaIpcMemHandle_t mine[4];
-    void *ptrs[4] = {h->pose[0], h->pose[1], h->lm_mean, h->lm_cov};
-    for (int j = 0; j < 4; j++) CU(cudaIpcGetMemHandle(&mine[j], ptrs[j]));
+    cudaIpcMemHandle_t mine[6];
+    void *ptrs[6] = {h->pose[0], h->pose[1], h->lm_mean, h->lm_cov, h->cdf, h->mloc};
+    for (int j = 0; j < 6; j++) CU(cudaIpcGetMemHandle(&mine[j], ptrs[j]));
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is 64 bytes");
-    const size_t per = sizeof(mine);  // 256 B per rank
+    const size_t per = sizeof(mine);  // 384 B per rank
     CU(cudaMemcpyAsync(c->d_small + (size_t) c->rank * per, mine, per, cudaMemcpyHostToDevice, h->stream));
     NC(g_nccl.AllGather(c->d_small + (size_t) c->rank * per, c->d_small, per, ncclChar, c->comm, h->stream));
     CU(cudaMemcpyAsync(c->h_small, c->d_small, per * c->world, cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     for (int r = 0; r < c->world; r++) {
-        void *p[4];
+        void *p[6];
         if (r == c->rank) {
-            for (int j = 0; j < 4; j++) p[j] = ptrs[j];
+            for (int j = 0; j < 6; j++) p[j] = ptrs[j];
         } else {
-            cudaIpcMemHandle_t hd[4];
+            cudaIpcMemHandle_t hd[6];
             memcpy(hd, c->h_small + (size_t) r * per, per);
-            for (int j = 0; j < 4; j++) {
+            for (int j = 0; j < 6; j++) {
                 CU(cudaIpcOpenMemHandle(&p[j], hd[j], cudaIpcMemLazyEnablePeerAccess));
                 c->opened[r][j] = p[j];
             }
@@ -168,6 +168,8 @@ static int open_peers(SlamComm *c, slamgpu *h) {
         c->peers.pose[1][r] = (const float *) p[1];
         c->peers.mean[r] = (const float2 *) p[2];
         c->peers.cov[r] = (const float4 *) p[3];
+        c->peers.cdf[r] = (const float *) p[4];
+        c->peers.mloc[r] = (const float *) p[5];
     }
     c->peers.world = c->world;
     c->peers_open = true;
@@ -181,6 +183,18 @@ int comm_peer_maps(SlamComm *c, slamgpu *h, PeerMaps *out) {
 }
 
 int comm_barrier(SlamComm *c, cudaStream_t st) { return barrier(c, st); }
+
+// Consecutive small exchanges issued between these two calls go out as ONE NCCL launch.
+int comm_group_begin(SlamComm *c) {
+    (void) c;
+    NC(g_nccl.GroupStart());
+    return SLAMGPU_OK;
+}
+int comm_group_end(SlamComm *c) {
+    (void) c;
+    NC(g_nccl.GroupEnd());
+    return SLAMGPU_OK;
+}
 
 int comm_allgather_i32(SlamComm *c, int *buf, size_t count, cudaStream_t st) {
     NC(g_nccl.AllGather(buf + (size_t) c->rank * count, buf, count, ncclInt32, c->comm, st));

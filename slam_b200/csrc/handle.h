@@ -132,5 +132,7 @@ int comm_halo_unif(SlamComm *c, double *unif_base, size_t P, cudaStream_t st);
 int comm_peer_maps(SlamComm *c, slamgpu *h, PeerMaps *out);
 // Stream-ordered barrier over all ranks (nobody passes until every rank's stream has reached it).
 int comm_barrier(SlamComm *c, cudaStream_t st);
+int comm_group_begin(SlamComm *c);
+int comm_group_end(SlamComm *c);
 int comm_allgather_i32(SlamComm *c, int *buf, size_t count, cudaStream_t st);
 int comm_reduce_estimate(SlamComm *c, slamgpu *h, double *sx, double *sy, float wmax, long long imax, double *theta);

@@ -197,7 +197,8 @@ __device__ __forceinline__ void lm_load_at(const float2 *mp, const float4 *cp, f
 template <bool REMAP>
 __device__ __forceinline__ void fs2_update_particle_reference_order(PoseSoA s, MapRing m, size_t P, size_t p,
                                                                     const float2 *sz, const unsigned long long *soff,
-                                                                    const unsigned long long *doff, long long q,
+                                                                    const unsigned long long *doff,
+                                                                    const float2 *smean, const float4 *scov,
                                                                     int K, float4 Rm, const float *gauss) {
     const float R[4] = {Rm.x, Rm.y, Rm.z, Rm.w};
     float x[3], C[9], x0[3], C0[9];
@@ -207,8 +208,8 @@ __device__ __forceinline__ void fs2_update_particle_reference_order(PoseSoA s, M
     const float g3[3] = {gauss[p], gauss[P + p], gauss[2 * P + p]};
     float xf[2], Pf[4];
     for (int i = 0; i < K; i++) {
-        const size_t src = soff[i] + ((REMAP && soff[i] != doff[i]) ? (size_t) q : p);
-        lm_load_at(m.mean + src, m.cov + src, xf, Pf);
+        const bool stale = REMAP && soff[i] != doff[i];
+        lm_load_at((stale ? smean : m.mean + p) + soff[i], (stale ? scov : m.cov + p) + soff[i], xf, Pf);
         const float z[2] = {sz[i].x, sz[i].y};
         proposal_step(x, C, R, xf, Pf, z);
     }
@@ -220,9 +221,9 @@ __device__ __forceinline__ void fs2_update_particle_reference_order(PoseSoA s, M
     const float prop = gauss_evaluate<3>(v2, C);
     float like = 1.0f;
     for (int i = 0; i < K; i++) {
-        const size_t src = soff[i] + ((REMAP && soff[i] != doff[i]) ? (size_t) q : p);
+        const bool stale = REMAP && soff[i] != doff[i];
         const size_t dst = (REMAP ? doff[i] : soff[i]) + p;
-        lm_load_at(m.mean + src, m.cov + src, xf, Pf);
+        lm_load_at((stale ? smean : m.mean + p) + soff[i], (stale ? scov : m.cov + p) + soff[i], xf, Pf);
         const float z[2] = {sz[i].x, sz[i].y};
         like = like * likelihood_and_feature_update(xs, R, xf, Pf, z);
         __stcs(m.mean + dst, make_float2(xf[0], xf[1]));
@@ -265,15 +266,23 @@ __device__ __forceinline__ void stage_obs_fs2(unsigned char *base, const ObsSet 
 
 // anc: the resample's keep[] (or a composed ancestor map) for this device's slots; -1 means "the last particle"
 // exactly as in k_gather_pose (core.cpp:800-806 leaves -1 where select ran past the CDF).
-__device__ __forceinline__ long long remap_column(const int *__restrict__ anc, size_t p, size_t P) {
+__device__ __forceinline__ long long remap_column(const int *__restrict__ anc, size_t p, long long n_global) {
     const int k = anc[p];
-    return k < 0 ? (long long) P - 1 : (long long) k;
+    return k < 0 ? n_global - 1 : (long long) k;
+}
+// The ancestor's column as pointers into the pool of the rank that holds it (global index q; rank = q / P).
+__device__ __forceinline__ void remap_source(const PeerRows &pr, long long q, size_t P, const float2 *&smean,
+                                             const float4 *&scov) {
+    const int r = (pr.world > 1) ? (int) (q / (long long) P) : 0;
+    const long long ql = q - (long long) r * (long long) P;
+    smean = pr.mean[r] + ql;
+    scov = pr.cov[r] + ql;
 }
 
 template <bool REMAP>
 __global__ void __launch_bounds__(128) k_fs2_update_listed(PoseSoA s, MapRing m, size_t P, ObsSet o, int K, float4 Rm,
                                                            const float *__restrict__ gauss,
-                                                           const int *__restrict__ anc,
+                                                           const int *__restrict__ anc, PeerRows pr, long long n_global,
                                                            const int *__restrict__ list, const int *__restrict__ count) {
     float2 *sz;
     unsigned long long *soff, *doff;
@@ -281,8 +290,10 @@ __global__ void __launch_bounds__(128) k_fs2_update_listed(PoseSoA s, MapRing m,
     const int n = *count;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const size_t p = (size_t) list[i];
-        fs2_update_particle_reference_order<REMAP>(s, m, P, p, sz, soff, doff, REMAP ? remap_column(anc, p, P) : 0, K,
-                                                   Rm, gauss);
+        const float2 *smean = nullptr;
+        const float4 *scov = nullptr;
+        if (REMAP) remap_source(pr, remap_column(anc, p, n_global), P, smean, scov);
+        fs2_update_particle_reference_order<REMAP>(s, m, P, p, sz, soff, doff, smean, scov, K, Rm, gauss);
     }
 }
 
@@ -317,7 +328,8 @@ __device__ __forceinline__ void cp_async_wait() {
 template <bool REMAP>
 __global__ void __launch_bounds__(SLAM_UPDATE_THREADS) k_fs2_update_fast(PoseSoA s, MapRing m, size_t P, ObsSet o, int K,
                                                                          float4 Rm, const float *__restrict__ gauss,
-                                                                         const int *__restrict__ anc,
+                                                                         const int *__restrict__ anc, PeerRows pr,
+                                                                         long long n_global,
                                                                          int *__restrict__ list, int *__restrict__ count) {
     constexpr int D = SLAM_RING_DEPTH, T = SLAM_UPDATE_THREADS;
     float4 *const ring_cov = reinterpret_cast<float4 *>(slam_smem) + threadIdx.x;                // slot s at [s * T]
@@ -329,15 +341,18 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS) k_fs2_update_fast(PoseSoA
     if (p >= P) return;
     const float2 *const mean_p = m.mean + p;
     const float4 *const cov_p = m.cov + p;
-    const long long dq = REMAP ? remap_column(anc, p, P) - (long long) p : 0;  // column shift of a stale row's source
-#define SLAM_SRC_OFF(i) (REMAP ? (long long) soff[i] + ((soff[i] != doff[i]) ? dq : 0ll) : (long long) soff[i])
+    // a stale row (REMAP) is read at the ancestor's column, on whichever rank holds it
+    const float2 *smean = mean_p;
+    const float4 *scov = cov_p;
+    if (REMAP) remap_source(pr, remap_column(anc, p, n_global), P, smean, scov);
+#define SLAM_SRC_MEAN(i) (((REMAP && soff[i] != doff[i]) ? smean : mean_p) + soff[i])
+#define SLAM_SRC_COV(i) (((REMAP && soff[i] != doff[i]) ? scov : cov_p) + soff[i])
     // the first D-1 rows go in flight before anything else is looked at
 #pragma unroll
     for (int j = 0; j < D - 1; j++) {
         if (j < K) {
-            const long long off = SLAM_SRC_OFF(j);
-            cp_async_8(ring_mean + j * T, mean_p + off);
-            cp_async_16(ring_cov + j * T, cov_p + off);
+            cp_async_8(ring_mean + j * T, SLAM_SRC_MEAN(j));
+            cp_async_16(ring_cov + j * T, SLAM_SRC_COV(j));
         }
         cp_async_commit();
     }
@@ -362,9 +377,8 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS) k_fs2_update_fast(PoseSoA
             if (i < K) {
                 const int j = i + D - 1;
                 if (j < K) {
-                    const long long noff = SLAM_SRC_OFF(j);
-                    cp_async_8(ring_mean + ((sl + D - 1) % D) * T, mean_p + noff);
-                    cp_async_16(ring_cov + ((sl + D - 1) % D) * T, cov_p + noff);
+                    cp_async_8(ring_mean + ((sl + D - 1) % D) * T, SLAM_SRC_MEAN(j));
+                    cp_async_16(ring_cov + ((sl + D - 1) % D) * T, SLAM_SRC_COV(j));
                 }
                 cp_async_commit();
                 cp_async_wait<D - 1>();  // one group per row: all but the newest D-1 have landed, row i among them
@@ -391,9 +405,8 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS) k_fs2_update_fast(PoseSoA
                 lm_load_at(ring_mean + sl * T, ring_cov + sl * T, xf, Pf);
                 const unsigned long long off = doff[i];
                 if (i - D >= 0) {  // the slot just read takes row i - D
-                    const long long noff = SLAM_SRC_OFF(i - D);
-                    cp_async_8(ring_mean + sl * T, mean_p + noff);
-                    cp_async_16(ring_cov + sl * T, cov_p + noff);
+                    cp_async_8(ring_mean + sl * T, SLAM_SRC_MEAN(i - D));
+                    cp_async_16(ring_cov + sl * T, SLAM_SRC_COV(i - D));
                 }
                 cp_async_commit();
                 const float z[2] = {sz[i].x, sz[i].y};
@@ -406,7 +419,8 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS) k_fs2_update_fast(PoseSoA
     s.w[p] = s.w[p] * like * ratio;
     const float Z[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
     store_pose(s, P, p, xs, Z);
-#undef SLAM_SRC_OFF
+#undef SLAM_SRC_MEAN
+#undef SLAM_SRC_COV
 }
 
 __global__ void __launch_bounds__(256) k_fs1_update_fast(PoseSoA s, MapRing m, size_t P, ObsSet o, int K, float4 Rm) {
@@ -700,8 +714,11 @@ __global__ void __launch_bounds__(SLAM_SCAN_BLOCK) k_cdf_finalise(float *__restr
 struct SearchArgs {
     const float *di;       // [n_local] strata midpoints for this device's global slots
     const double *unif;    // [n_local]
-    const float *cdf;      // [n_global] (all-gathered when sharded)
-    const float *mloc;     // [n_global]
+    const float *cdf[SLAM_MAX_RANKS];   // [n_global]-indexed per rank; rank r = index / n_local holds that block.  When
+    const float *mloc[SLAM_MAX_RANKS];  // sharded these are the peers' buffers themselves (CUDA IPC over NVLink): a
+                                        // slot's search lands on its own rank unless the weights are badly skewed, so
+                                        // the two 4*Pg-byte all-gathers of the first version bought nothing
+    int world;
     const float *BM;       // [nb_global] prefix maxima of the block maxima
     float *sel;            // [n_local] out
     int *keep;             // [n_local] out (global indices)
@@ -727,10 +744,12 @@ __device__ __forceinline__ long long first_exceed(const SearchArgs &a, float s) 
     if (lo == a.nb_global) return (long long) a.n_global;  // sentinel: never assigned
     const size_t b0 = (size_t) lo * SLAM_SCAN_BLOCK;
     const int len = (int) min((size_t) SLAM_SCAN_BLOCK, a.n_global - b0);
+    // a 1024-block never straddles two ranks (n_local is a multiple of 1024 when sharded)
+    const float *mloc = a.mloc[a.world > 1 ? (int) (b0 / a.n_local) : 0];
     int l = 0, h = len - 1;  // the block's last running max exceeds s, so an answer exists
     while (l < h) {
         const int mid = (l + h) >> 1;
-        if (a.mloc[b0 + mid] > s) h = mid; else l = mid + 1;
+        if (mloc[b0 + mid] > s) h = mid; else l = mid + 1;
     }
     return (long long) (b0 + l);
 }
@@ -771,7 +790,7 @@ __global__ void __launch_bounds__(256) k_search_keep(SearchArgs a) {
     const long long SENT = (long long) a.n_global;
     bool ok;
     if (g >= kprev) ok = true;
-    else ok = (kc == kprev) && (kprev == SENT || a.cdf[kprev] > s);
+    else ok = (kc == kprev) && (kprev == SENT || a.cdf[a.world > 1 ? (int) ((size_t) kprev / a.n_local) : 0][kprev] > s);
     if (!ok) atomicExch(a.anomaly, 1);
     a.keep[c] = (kc == SENT) ? -1 : (int) kc;
 }

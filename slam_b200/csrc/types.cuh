@@ -25,6 +25,14 @@ struct PeerMaps {  // this device's and (when sharded) the peers' buffers, index
     const float *pose[2][SLAM_MAX_RANKS];
     const float2 *mean[SLAM_MAX_RANKS];
     const float4 *cov[SLAM_MAX_RANKS];
+    const float *cdf[SLAM_MAX_RANKS];   // each rank's [Pg]-indexed CDF / running-maximum buffers (its own block filled)
+    const float *mloc[SLAM_MAX_RANKS];
+    int world;
+};
+
+struct PeerRows {  // landmark pools by rank, for kernels that read a particle's ancestor column wherever it lives
+    const float2 *mean[SLAM_MAX_RANKS];
+    const float4 *cov[SLAM_MAX_RANKS];
     int world;
 };
 

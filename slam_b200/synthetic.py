@@ -22,17 +22,21 @@ SYNTH_SIGMA_B = 5.0 * np.pi / 180
 
 
 def synthetic_state(P, Nf, K, seed=1, extent=100.0, nf_cap=None, sigma_r=SYNTH_SIGMA_R, sigma_b=SYNTH_SIGMA_B,
-                    particle_spread=0.1):
+                    particle_spread=0.1, map_seed=None):
     """Returns dict of flat arrays + one observation set.
 
     Map: Nf landmarks uniform in [-extent, extent]^2; true pose (0,0,0); particle poses = true pose +
     N(0, diag(0.05^2, 0.05^2, (0.5deg)^2)); Pv = a fixed SPD matrix typical of 8 predict ticks;
     landmark cov = Gz R Gz^T of addFeature (core.cpp:498-500), landmark means = truth + N(0, cov) common to
     all particles + particle_spread * N(0, cov) per particle.
+
+    map_seed: when given, the map and the common map error come from their own generator, so that shards built with
+    different `seed`s (different particles per rank) still share ONE world and hence one observation sequence.
     """
     rng = np.random.default_rng(seed)
+    rng_map = rng if map_seed is None else np.random.default_rng(map_seed)
     nf_cap = nf_cap or Nf
-    lm = rng.uniform(-extent, extent, (Nf, 2)).astype(np.float32)
+    lm = rng_map.uniform(-extent, extent, (Nf, 2)).astype(np.float32)
     xv = np.zeros((3, P), np.float32)
     xv[0] = rng.normal(0, 0.05, P)
     xv[1] = rng.normal(0, 0.05, P)
@@ -53,7 +57,7 @@ def synthetic_state(P, Nf, K, seed=1, extent=100.0, nf_cap=None, sigma_r=SYNTH_S
         L = np.linalg.cholesky(C + 1e-12 * np.eye(2))
         # map error mostly common to all particles (it is correlated through the shared trajectory), plus a
         # smaller per-particle part: keeps the weights of a K = 32 update from collapsing onto a few particles
-        common = rng.standard_normal(2) @ L.T
+        common = rng_map.standard_normal(2) @ L.T
         lm_mean[l] = lm[l] + (common + particle_spread * (rng.standard_normal((P, 2)) @ L.T)).astype(np.float32)
         lm_cov[l] = np.array([C[0, 0], C[1, 0], C[0, 1], C[1, 1]], np.float32)
     lm_mean[Nf:] = 0

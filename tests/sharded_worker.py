@@ -88,7 +88,52 @@ def main():
             st = [(s.xv.copy(), s.Pv.copy(), s.lm_mean.copy(), s.lm_cov.copy())]
         dist.broadcast_object_list(st, 0)
         s.xv[:], s.Pv[:], s.lm_mean[:], s.lm_cov[:] = st[0]
+    # ---- phase 2: observed rows re-columned INSIDE the update kernel, ancestors on peer devices ----------------
+    # No map download between a resample and the next update, so the sharded handles take the fused path
+    # (kernels.cuh K3 REMAP, sources read through the peer mappings).  Rank 0 also drives a ONE-device handle holding
+    # all Pg particles with a single spare row (separate gather kernels, no fusion): per-particle arithmetic does not
+    # depend on the sharding and the blocked resample is bit-identical for any device count, so after 4 cycles the
+    # two must agree bit for bit.
+    f.close()
+    f = slam_b200.FastSLAM(slam_b200.FASTSLAM2, Pl, Nf, wheel_base=WHEELBASE, sigma_phi=SIGMA_PHI,
+                           n_effective=Pg + 1, use_heading=True, scan_mode=slam_b200.SCAN_BLOCKED, device=local)
+    dist.broadcast(idbuf.zero_() if rank else idbuf.copy_(torch.frombuffer(
+        bytearray(slam_b200.FastSLAM.comm_unique_id()), dtype=torch.uint8)), 0)
+    f.comm_init(rank, world, idbuf.cpu().numpy().tobytes())
+    f.upload(c(d["xv"][:, sl]), c(d["Pv"][:, sl]), c(d["w"][sl]), c(d["lm_mean"][:, sl]), c(d["lm_cov"][:, sl]), Nf)
+    f1 = None
     if rank == 0:
+        f1 = slam_b200.FastSLAM(slam_b200.FASTSLAM2, Pg, Nf, wheel_base=WHEELBASE, sigma_phi=SIGMA_PHI,
+                                n_effective=Pg + 1, use_heading=True, scan_mode=slam_b200.SCAN_BLOCKED, device=local,
+                                spare_rows=1)
+        f1.upload(d["xv"], d["Pv"], d["w"], d["lm_mean"], d["lm_cov"], Nf)
+    for cycle in range(4):
+        for _ in range(2):
+            V, G, dt, phi = drive.controls()
+            f.predict(V, G, Q_DEFAULT, dt, phi)
+            if f1:
+                f1.predict(V, G, Q_DEFAULT, dt, phi)
+        zf, idf = drive.observe()
+        gauss = rng.standard_normal((3, Pg)).astype(np.float32)
+        unif = rng.random(Pg)
+        f.update_particles(zf, idf, np.zeros((0, 2), np.float32), d["R"], c(gauss[:, sl]))
+        keep, neff, did = f.resample(c(unif[sl]), want_keep=True)
+        assert did
+        if f1:
+            f1.update_particles(zf, idf, np.zeros((0, 2), np.float32), d["R"], gauss)
+            keep1, neff1, did1 = f1.resample(unif, want_keep=True)
+            assert did1 and neff1 == neff and np.array_equal(keep1[sl], keep), "phase 2 cycle %d keep[]" % cycle
+    assert f.stats()["rows_fused"] >= 3 * (K - 1), f.stats()
+    g = f.download()
+    dist.all_gather_object(parts, g)
+    if rank == 0:
+        g1 = f1.download()
+        assert f1.stats()["rows_fused"] == 0
+        for k in ("xv", "Pv", "w", "lm_mean", "lm_cov"):
+            got = np.concatenate([p[k] for p in parts], axis=(0 if k == "w" else 1))
+            assert np.array_equal(got, g1[k]), "phase 2 (fused, sharded) vs one device: " + k
+        assert np.isfinite(g1["lm_mean"]).all()
+        f1.close()
         print("SHARDED_OK world=%d" % world)
     f.close()
     dist.destroy_process_group()
