@@ -150,6 +150,10 @@ class FastSLAM:
             assert g.shape == (2, self.P)
         self._check(self._L.slamgpu_predict(self._h, V, G, _ptr(Q), dt, phi_true, _ptr(g)))
 
+    def predict_raw(self, V, G, Q_ptr, dt, phi_true=0.0):
+        """predict() without control noise on a raw host address for Q (no numpy marshalling)."""
+        self._check(self._L.slamgpu_predict(self._h, V, G, Q_ptr, dt, phi_true, None))
+
     def _obs(self, zf, idf, zn):
         zf = _f32(np.asarray(zf, np.float32).reshape(-1, 2))
         zn = _f32(np.asarray(zn, np.float32).reshape(-1, 2))

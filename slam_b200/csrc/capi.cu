@@ -102,6 +102,9 @@ static void free_all(slamgpu *h) {
     for (auto e : h->free_events) cudaEventDestroy(e);
     for (auto e : h->obs_ev)
         if (e) cudaEventDestroy(e);
+    for (auto e : {h->ev_in, h->ev_gauss, h->ev_unif})
+        if (e) cudaEventDestroy(e);
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     void *dev[] = {h->pose[0], h->pose[1], h->w, h->lm_mean, h->lm_cov, h->gauss, h->unif_base, h->di_base, h->cdf,
                    h->mloc, h->sel, h->keep, h->tot_w, h->tot_c, h->tot_s, h->bmax, h->d_sc, h->d_z,
                    h->d_rec_in, h->d_rec_out, h->d_est, h->keeplog, h->anc, h->d_phys, h->fb_list, h->fb_count};
@@ -654,6 +657,9 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
     if (fs2 && (K > 0 || Kn > 0)) {
         if (gauss) {
             CU(cudaMemcpyAsync(h->gauss, gauss, sizeof(float) * 3 * h->P, cudaMemcpyHostToDevice, h->stream));
+        } else if (h->gauss_inflight) {  // slamgpu_update put the copy on the copy stream: it overlaps the predict pass
+            CU(cudaStreamWaitEvent(h->stream, h->ev_gauss, 0));
+            h->gauss_inflight = false;
         } else if (!(h->gauss_staged && h->gauss_rows_staged == 3)) {
             return slam_fail(SLAMGPU_EINVAL, "FastSLAM2 update needs gauss[3][P] (or slamgpu_stage_noise first)");
         }
@@ -887,6 +893,9 @@ extern "C" int slamgpu_resample(slamgpu_t *h, const double *unif, int32_t *keep_
     RET(flush_predicts(h));
     if (unif) {
         CU(cudaMemcpyAsync(h->unif(), unif, sizeof(double) * h->P, cudaMemcpyHostToDevice, h->stream));
+    } else if (h->unif_inflight) {  // copied by slamgpu_update on the copy stream while the update kernel ran
+        CU(cudaStreamWaitEvent(h->stream, h->ev_unif, 0));
+        h->unif_inflight = false;
     } else if (!h->unif_staged) {
         return slam_fail(SLAMGPU_EINVAL, "resample needs unif[P] (or slamgpu_stage_noise first)");
     }
@@ -920,8 +929,40 @@ extern "C" int slamgpu_resample(slamgpu_t *h, const double *unif, int32_t *keep_
 extern "C" int slamgpu_update(slamgpu_t *h, const float *zf, const int32_t *idf, int32_t K, const float *zn,
                               int32_t Kn, const float R[4], const float *gauss, const double *unif,
                               int32_t *did_resample, float *neff) {
-    RET(slamgpu_update_particles(h, zf, idf, K, zn, Kn, R, gauss));
-    return slamgpu_resample(h, unif, nullptr, neff, did_resample);
+    if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
+    // Host noise goes up on a second stream: the 12 B/particle of Gaussians overlap the predict pass, the 8 B/particle
+    // of resample uniforms overlap the whole update kernel (they are first read by the search that follows it).
+    const bool want_gauss = gauss && h->cfg.method == SLAMGPU_FASTSLAM2 && (K > 0 || Kn > 0);
+    if (want_gauss || unif) {
+        CU(cudaSetDevice(h->cfg.device));
+        if (!h->copy_stream) {
+            CU(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+            CU(cudaEventCreateWithFlags(&h->ev_in, cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&h->ev_gauss, cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&h->ev_unif, cudaEventDisableTiming));
+        }
+        CU(cudaEventRecord(h->ev_in, h->stream));  // earlier readers of the two buffers are behind this point
+        CU(cudaStreamWaitEvent(h->copy_stream, h->ev_in, 0));
+        if (want_gauss) {
+            CU(cudaMemcpyAsync(h->gauss, gauss, sizeof(float) * 3 * h->P, cudaMemcpyHostToDevice, h->copy_stream));
+            CU(cudaEventRecord(h->ev_gauss, h->copy_stream));
+            h->gauss_inflight = true;
+            h->gauss_staged = false;
+        }
+        if (unif) {
+            CU(cudaMemcpyAsync(h->unif(), unif, sizeof(double) * h->P, cudaMemcpyHostToDevice, h->copy_stream));
+            CU(cudaEventRecord(h->ev_unif, h->copy_stream));
+            h->unif_inflight = true;
+            h->unif_staged = false;
+        }
+    }
+    int rc = slamgpu_update_particles(h, zf, idf, K, zn, Kn, R, nullptr);
+    if (rc == SLAMGPU_OK) rc = slamgpu_resample(h, nullptr, nullptr, neff, did_resample);
+    if (rc != SLAMGPU_OK) {  // never leave a copy racing with the caller's buffers
+        if (h->copy_stream) cudaStreamSynchronize(h->copy_stream);
+        h->gauss_inflight = h->unif_inflight = false;
+    }
+    return rc;
 }
 
 // ---- computeJacobians ---------------------------------------------------------------------------------------

@@ -89,6 +89,10 @@ struct slamgpu {
     EstPartial *d_est = nullptr, *h_est = nullptr;
     int est_blocks = 0;
     bool gauss_staged = false, unif_staged = false;
+    // slamgpu_update's host noise travels on a second stream (capi.cu)
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_in = nullptr, ev_gauss = nullptr, ev_unif = nullptr;
+    bool gauss_inflight = false, unif_inflight = false;
     int gauss_rows_staged = 0;
     // timing
     bool timing = false;
