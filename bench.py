@@ -380,8 +380,15 @@ def run_ours(a):
     kern = {"update": "k_fs2_update_fast<REMAP> (cp.async landmark ring)", "gather": "k_gather_pose + k_chain + k_materialise_rows",
             "predict": "k_predict_batch_fast",
             "weights": "scan/search kernels"}[top]
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "r01_fs2_update_traffic.json")
+    if top == "update" and (P, Nf, K) == (1 << 20, 1024, 32) and os.path.exists(tp):
+        try:  # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture
+            traffic = json.load(open(tp))["dram_bytes_per_launch"]
+        except Exception:
+            traffic = None
     roofline = {"bound": "hbm", "kernel": kern, "achieved": roof.get(top, {}).get("achieved"), "peak": peak,
-                "unit": "GB/s", "frac": roof.get(top, {}).get("frac"), "traffic": None, "peak_source": peak_src,
+                "unit": "GB/s", "frac": roof.get(top, {}).get("frac"), "traffic": traffic, "peak_source": peak_src,
                 "families": roof, "family_ms_total": fam_ms}
 
     cpu = None
