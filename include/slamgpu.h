@@ -186,6 +186,42 @@ int64_t slamgpu_launch_count(slamgpu_t *h);
 int slamgpu_comm_unique_id(void *id128);
 int slamgpu_comm_init(slamgpu_t *h, int32_t rank, int32_t world, const void *id128);
 
+
+/* ---- EKF-SLAM entry point (the reference's third -method, algorithms/ekfslam.h:14-56) -----------------------
+ * One joint state x = [pose; landmarks] (n = 3 + 2*Nf) with its dense n x n covariance, resident on the device.
+ * slamgpu_ekf_sim is EKFSLAM::sim (ekfslam.cpp:18-43): predict, optional compass update (observeHeading), and when
+ * `observe` the association (gated nearest neighbour, or the known table), batchUpdate and augment.  Matrices cross
+ * the ABI row-major.  Like the reference's wrapper (ekfslamwrapper.cpp:80-83: zf, idf, zn and the association table
+ * are passed BY VALUE) the table is read-only here; the association made by the call is reported back. */
+typedef struct slamgpu_ekf slamgpu_ekf_t;
+typedef struct slamgpu_ekf_config {
+    int32_t nf_cap;            /* landmarks the state can grow to */
+    int32_t m_cap;             /* most observations per call (0 = 64) */
+    float wheel_base;          /* WHEELBASE */
+    float sigma_phi;           /* sigmaT */
+    float gate_reject;         /* GATE_REJECT  (ekfslam.cpp:172) */
+    float gate_augment;        /* GATE_AUGMENT (ekfslam.cpp:184) */
+    int32_t use_heading;       /* SWITCH_HEADING_KNOWN */
+    int32_t batch_update;      /* SWITCH_BATCH_UPDATE */
+    int32_t association_known; /* SWITCH_ASSOCIATION_KNOWN */
+    int32_t device;
+    int32_t reserved[4];
+} slamgpu_ekf_config;
+int slamgpu_ekf_create(const slamgpu_ekf_config *cfg, slamgpu_ekf_t **out); /* x = 0, P = zeros(3,3) */
+void slamgpu_ekf_destroy(slamgpu_ekf_t *h);
+/* z [m][2] range/bearing of the visible landmarks (landmarksRangeBearing), idz [m] their identifiers and table [ntab]
+ * (only read when association_known).  Qe / Re / R row-major 2x2 (Re gates and augments, R updates: ekfslam.cpp:34-41).
+ * Out (nullable): idf_out [<= m] map slots of the associated observations in call order, their count, and the
+ * number of new landmarks appended. */
+int slamgpu_ekf_sim(slamgpu_ekf_t *h, float V, float G, const float Qe[4], float dt, float phi, int32_t observe,
+                    const float *z, const int32_t *idz, int32_t m, const int32_t *table, int32_t ntab,
+                    const float Re[4], const float R[4], int32_t *idf_out, int32_t *n_zf, int32_t *n_zn);
+int slamgpu_ekf_size(slamgpu_ekf_t *h); /* n = x.size() */
+int slamgpu_ekf_set_state(slamgpu_ekf_t *h, int32_t n, const float *x, const float *P);
+int slamgpu_ekf_get_state(slamgpu_ekf_t *h, float *x, float *P); /* x [n], P [n][n]; either may be NULL */
+int slamgpu_ekf_get_pose(slamgpu_ekf_t *h, float xv[3], float Pvv[9]); /* per-tick plot feed, ekfslamwrapper.cpp:91-101 */
+int64_t slamgpu_ekf_launch_count(slamgpu_ekf_t *h);
+
 #ifdef __cplusplus
 }
 #endif

@@ -3,3 +3,4 @@ mirror of the reference's FastSLAM1/FastSLAM2 method objects.  See DESIGN.md."""
 from .backend import (FASTSLAM1, FASTSLAM2, MATH_FAST, MATH_REFERENCE_ORDER, SCAN_BLOCKED, SCAN_REFERENCE, FastSLAM, SlamGpuError,  # noqa: F401
                       compute_jacobians)
 from .build import build  # noqa: F401
+from .ekf import EKFSLAM  # noqa: F401

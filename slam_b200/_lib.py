@@ -15,7 +15,16 @@ EXPORTS = [
     "slamgpu_compute_jacobians", "slamgpu_compute_jacobians_batch", "slamgpu_estimate", "slamgpu_download_decimated",
     "slamgpu_timing_enable", "slamgpu_timing_read", "slamgpu_timing_reset", "slamgpu_launch_count", "slamgpu_stat",
     "slamgpu_comm_unique_id", "slamgpu_comm_init",
+    "slamgpu_ekf_create", "slamgpu_ekf_destroy", "slamgpu_ekf_sim", "slamgpu_ekf_size", "slamgpu_ekf_set_state",
+    "slamgpu_ekf_get_state", "slamgpu_ekf_get_pose", "slamgpu_ekf_launch_count",
 ]
+
+
+class EkfConfig(C.Structure):
+    _fields_ = [("nf_cap", C.c_int32), ("m_cap", C.c_int32), ("wheel_base", C.c_float), ("sigma_phi", C.c_float),
+                ("gate_reject", C.c_float), ("gate_augment", C.c_float), ("use_heading", C.c_int32),
+                ("batch_update", C.c_int32), ("association_known", C.c_int32), ("device", C.c_int32),
+                ("reserved", C.c_int32 * 4)]
 
 
 class Config(C.Structure):
@@ -37,6 +46,17 @@ def load():
                            "slam_b200 has no fallback path")
     L = C.CDLL(LIB_PATH)
     vp, fp, ip, dp = C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p  # raw addresses; wrappers pass numpy .ctypes.data
+    L.slamgpu_ekf_create.argtypes = [C.POINTER(EkfConfig), C.POINTER(vp)]
+    L.slamgpu_ekf_destroy.argtypes = [vp]
+    L.slamgpu_ekf_destroy.restype = None
+    L.slamgpu_ekf_sim.argtypes = [vp, C.c_float, C.c_float, fp, C.c_float, C.c_float, C.c_int32, fp, ip, C.c_int32, ip,
+                                  C.c_int32, fp, fp, ip, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    L.slamgpu_ekf_size.argtypes = [vp]
+    L.slamgpu_ekf_set_state.argtypes = [vp, C.c_int32, fp, fp]
+    L.slamgpu_ekf_get_state.argtypes = [vp, fp, fp]
+    L.slamgpu_ekf_get_pose.argtypes = [vp, fp, fp]
+    L.slamgpu_ekf_launch_count.argtypes = [vp]
+    L.slamgpu_ekf_launch_count.restype = C.c_int64
     L.slamgpu_last_error.restype = C.c_char_p
     L.slamgpu_version.restype = C.c_char_p
     L.slamgpu_create.argtypes = [C.POINTER(Config), C.POINTER(vp)]
