@@ -1,6 +1,8 @@
 // slam-backend-gpu — command-line twin of the reference's `slam-backend` (src/backend/slam-backend.cpp,
 // SLAMBackendApplication.cpp:59-89): same options, same <map>.ini next to the map, same precedence
 // (defaults <- ini <- "-KEY value" for any key), method fall-through to EKF.  Extra options of this build:
+//   -plot ENDPOINT  feed the reference's slam-gui over its zmq protocol ("default" = tcp://127.0.0.1:4242, the address
+//                   the reference hard-codes; the reference always connects, here it is opt-in)
 //   -trace FILE     write the per-iteration true / estimated pose (the plot feed without a GUI)
 //   -max_iter N     stop after N iterations
 //   -device D       CUDA device ordinal
@@ -72,6 +74,18 @@ int main(int argc, char **argv) {
             fprintf(stderr, "cannot open trace file %s\n", conf.s("trace").c_str());
             return EXIT_FAILURE;
         }
+    }
+    if (!conf.s("plot").empty()) {
+        std::string e;
+        const std::string ep = conf.s("plot") == "default" ? "tcp://127.0.0.1:4242" : conf.s("plot");
+        PlotSink *zp = make_zmq_plot(ep, name, &e);
+        if (!zp) {
+            fprintf(stderr, "%s\n", e.c_str());
+            return EXIT_FAILURE;
+        }
+        if (sink) sink.reset(make_tee_plot(sink.release(), zp));
+        else sink.reset(zp);
+        if (opt.plot_stride == 0) opt.plot_stride = conf.NPARTICLES > 2000 ? conf.NPARTICLES / 1000 : 1;
     }
     const std::string method = conf.s("method");
     RunResult r;

@@ -70,10 +70,18 @@ struct PlotSink {
     // one call per loop iteration, after the algorithm step
     virtual void tick(int iteration, const float x_true[3], const double x_est[3], int n_obs, uint32_t loop_us) {}
     virtual void particles(const float *xv, int64_t n, const float *lm_mean, int nf) {}  // decimated feed (xv [3][n])
+    virtual void laser(const float *z, int n, const float x_true[3]) {}  // range / bearing of the last observation
+    virtual bool wants_ellipses() { return false; }                      // EKF: covariance ellipses cost a state download
+    virtual void ellipse(const double xy[2], const float P[4], int idx) {}
     virtual void end() {}
 };
 // Writes "iteration x_true y_true t_true x_est y_est t_est n_obs" lines; the GUI-less trace the tests read.
 PlotSink *make_trace_plot(const std::string &path);
+// The reference's NetworkPlot wire protocol (plotting/NetworkPlot.cpp) over a ZMQ_PAIR socket connected to `endpoint`
+// (the reference hard-codes tcp://127.0.0.1:4242); libzmq is dlopen()ed.  nullptr + *err on failure.
+PlotSink *make_zmq_plot(const std::string &endpoint, const std::string &simulation_name, std::string *err);
+// Both at once (trace file + GUI).
+PlotSink *make_tee_plot(PlotSink *a, PlotSink *b);
 
 // ---- the run loops (wrappers/fastslam1wrapper.cpp, fastslam2wrapper.cpp, ekfslamwrapper.cpp) -------------------------
 struct RunOptions {

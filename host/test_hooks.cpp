@@ -98,4 +98,33 @@ int slamhost_data_association_known(const float *z, const int *idz, int m, int *
     return (int) idfv.size();
 }
 
+// Emits a fixed script through the zmq plot sink (no GPU involved): begin on the current map, one observation with two
+// laser lines, a 3-particle / 2-landmark feed, one covariance ellipse, one tick, end.  0 ok, -1 + err text otherwise.
+int slamhost_zmq_selftest(const char *endpoint, char *err, int cap) {
+    std::string e;
+    PlotSink *p = make_zmq_plot(endpoint, "selftest", &e);
+    if (!p) {
+        strncpy(err, e.c_str(), cap - 1);
+        err[cap - 1] = 0;
+        return -1;
+    }
+    Conf c;
+    c.parse();
+    p->begin(c, g_map, "FASTSLAM2");
+    const float xt[3] = {1.0f, 2.0f, 0.5f};
+    const float z[4] = {5.0f, 0.25f, 7.5f, -1.0f};
+    p->laser(z, 2, xt);
+    const float xv[9] = {0.1f, 0.2f, 0.3f, 1.1f, 1.2f, 1.3f, 0, 0, 0};                    // [3][n = 3]
+    const float lm[12] = {10, 11, 12, 13, 14, 15, 20, 21, 22, 23, 24, 25};                  // [nf = 2][n = 3][2]
+    p->particles(xv, 3, lm, 2);
+    const double cxy[2] = {1.0, 2.0};
+    const float P[4] = {0.04f, 0.01f, 0.01f, 0.09f};
+    p->ellipse(cxy, P, 0);
+    const double xe[3] = {1.25, 1.75, 0.45};
+    p->tick(1, xt, xe, 2, 1234u);
+    p->end();
+    delete p;
+    return 0;
+}
+
 }  // extern "C"

@@ -128,6 +128,7 @@ RunResult run_fastslam(int method, const Conf &conf, const Map &map, PlotSink *p
             sim.dtSum = 0;
             get_observations(map, sim.xTrue, conf.MAX_RANGE, &ids, &z);
             if (conf.SWITCH_SENSOR_NOISE) add_observation_noise(&z, sim.R);
+            if (plot) plot->laser(z.data(), (int) ids.size(), sim.xTrue);  // plines = makeLaserLines(...)
             const int Nf = slamgpu_landmark_count(h);
             data_association_known(z, ids, &table, Nf, &zf, &idf, &zn);
             const int K = (int) idf.size(), Kn = (int) zn.size() / 2;
@@ -207,7 +208,7 @@ RunResult run_ekfslam(const Conf &conf, const Map &map, PlotSink *plot, const Ru
         res.error = slamgpu_last_error();
         return res;
     }
-    std::vector<float> z;
+    std::vector<float> z, xs, Ps;
     std::vector<int> ids, table(n_lm, -1);
     if (plot) plot->begin(conf, map, "EKF1");
     int rc = SLAMGPU_OK, n_obs = 0;
@@ -223,6 +224,7 @@ RunResult run_ekfslam(const Conf &conf, const Map &map, PlotSink *plot, const Ru
             sim.dtSum = 0;
             get_observations(map, sim.xTrue, conf.MAX_RANGE, &ids, &z);
             if (conf.SWITCH_SENSOR_NOISE) add_observation_noise(&z, sim.R);
+            if (plot) plot->laser(z.data(), (int) ids.size(), sim.xTrue);
         }
         // landmarksRangeBearing keeps its last value between observations in the reference; sim only looks at it when
         // observe is set
@@ -242,6 +244,20 @@ RunResult run_ekfslam(const Conf &conf, const Map &map, PlotSink *plot, const Ru
         rc = slamgpu_ekf_get_pose(h, xv, nullptr);
         if (rc != SLAMGPU_OK) break;
         const double est[3] = {xv[0], xv[1], xv[2]};
+        if (plot && plot->wants_ellipses()) {  // drawCovarianceEllipseLines, ekfslamwrapper.cpp:117-136
+            const int n = slamgpu_ekf_size(h);
+            xs.resize(n);
+            Ps.resize((size_t) n * n);
+            rc = slamgpu_ekf_get_state(h, xs.data(), Ps.data());
+            if (rc != SLAMGPU_OK) break;
+            for (int b = 0; b < 1 + (n - 3) / 2; b++) {
+                const int o = b == 0 ? 0 : 3 + 2 * (b - 1);
+                const double c[2] = {xs[o], xs[o + 1]};
+                const float blk[4] = {Ps[(size_t) o * n + o], Ps[(size_t) o * n + o + 1], Ps[(size_t) (o + 1) * n + o],
+                                      Ps[(size_t) (o + 1) * n + o + 1]};
+                plot->ellipse(c, blk, b);
+            }
+        }
         if (plot) plot->tick(sim.currentIteration, sim.xTrue, est, n_obs, us);
         for (int i = 0; i < 3; i++) res.x_est[i] = est[i];
         if (opt.max_iterations > 0 && sim.currentIteration >= opt.max_iterations) break;
@@ -273,6 +289,25 @@ struct TracePlot : PlotSink {
     void end() override { fflush(fp); }
 };
 }  // namespace
+
+namespace {
+struct TeePlot : PlotSink {
+    PlotSink *a, *b;
+    TeePlot(PlotSink *x, PlotSink *y) : a(x), b(y) {}
+    ~TeePlot() override {
+        delete a;
+        delete b;
+    }
+    void begin(const Conf &c, const Map &m, const std::string &s) override { a->begin(c, m, s); b->begin(c, m, s); }
+    void tick(int i, const float t[3], const double e[3], int n, uint32_t us) override { a->tick(i, t, e, n, us); b->tick(i, t, e, n, us); }
+    void particles(const float *x, int64_t n, const float *l, int nf) override { a->particles(x, n, l, nf); b->particles(x, n, l, nf); }
+    void laser(const float *z, int n, const float x[3]) override { a->laser(z, n, x); b->laser(z, n, x); }
+    bool wants_ellipses() override { return a->wants_ellipses() || b->wants_ellipses(); }
+    void ellipse(const double xy[2], const float P[4], int i) override { a->ellipse(xy, P, i); b->ellipse(xy, P, i); }
+    void end() override { a->end(); b->end(); }
+};
+}  // namespace
+PlotSink *make_tee_plot(PlotSink *a, PlotSink *b) { return new TeePlot(a, b); }
 
 PlotSink *make_trace_plot(const std::string &path) {
     FILE *f = fopen(path.c_str(), "w");
