@@ -46,6 +46,7 @@ def parse():
     ap.add_argument("--tile", type=int, default=4096, help="distinct synthetic particles generated on the host")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--same-tile", action="store_true", help="experiment: every rank starts from the same particle tile")
     ap.add_argument("--ref-particles", type=int, default=1000, help="particles per reference instance (core.cpp:762 valid)")
     return ap.parse_args()
 
@@ -239,7 +240,7 @@ def run_ours(a):
     P, Nf, K = a.particles, a.landmarks, a.obs
     Pg = P * world
     tile = min(a.tile, P)
-    d = synthetic_state(tile, Nf, K, seed=1 + rank, map_seed=1)  # one world, different particles per rank
+    d = synthetic_state(tile, Nf, K, seed=1 if a.same_tile else 1 + rank, map_seed=1)  # one world, different particles per rank
     f = slam_b200.FastSLAM(slam_b200.FASTSLAM2, P, Nf, wheel_base=WHEELBASE, sigma_phi=SIGMA_PHI,
                            n_effective=int(0.75 * Pg), use_heading=True, scan_mode=slam_b200.SCAN_BLOCKED,
                            device=local)
@@ -340,6 +341,8 @@ def run_ours(a):
     rows_moved = stats1["rows_moved"] - stats0["rows_moved"]
     n_resamples = stats1["resamples"] - stats0["resamples"]
     rows_fused = stats1["rows_fused"] - stats0["rows_fused"]
+    remote = stats1["remote_sources"] - stats0["remote_sources"]
+    remote_frac = max_over_ranks(remote / max(1, n_resamples * P)) if world > 1 else 0.0
     fam = f.timing_read()
     f.timing_enable(False)
     resample_rate = state["resamples"] / max(1, state["steps"])
@@ -409,6 +412,8 @@ def run_ours(a):
                            "map_resampling": "deferred: %d landmark rows re-columned over %d resamples (eager copy: %d); "
                                              "%d of them inside the update kernel itself (fused, no extra pass)"
                                              % (rows_moved, n_resamples, n_resamples * Nf, rows_fused),
+                           "migration": "%.1f%% of resampled particles came from another GPU (worst rank)"
+                                        % (100 * remote_frac),
                            "predict": "the 8 ticks per step are queued and applied in one pass",
                            "noise": "pre-drawn on the host, %d sets rotated" % NPOOL},
                 "clocks": clk, "gpu_launches": int(launches),

@@ -173,6 +173,7 @@ int slamgpu_timing_reset(slamgpu_t *h);
 #define SLAMGPU_STAT_ROWS_MOVED 0
 #define SLAMGPU_STAT_RESAMPLES 1
 #define SLAMGPU_STAT_CHAIN_STEPS 2
+#define SLAMGPU_STAT_REMOTE_SOURCES 4 /* sharded: resampled slots whose particle came from another device */
 #define SLAMGPU_STAT_ROWS_FUSED 3 /* of ROWS_MOVED: re-columned inside the FastSLAM2 update kernel itself (no extra pass) */
 int64_t slamgpu_stat(slamgpu_t *h, int32_t which);
 /* Total kernel launches issued by this handle since creation. */

@@ -95,7 +95,8 @@ class FastSLAM:
     def stats(self):
         """rows re-columned by deferred resampling, resamples applied, ancestor-chain steps."""
         return dict(rows_moved=self._L.slamgpu_stat(self._h, 0), resamples=self._L.slamgpu_stat(self._h, 1),
-                    chain_steps=self._L.slamgpu_stat(self._h, 2), rows_fused=self._L.slamgpu_stat(self._h, 3))
+                    chain_steps=self._L.slamgpu_stat(self._h, 2), rows_fused=self._L.slamgpu_stat(self._h, 3),
+                    remote_sources=self._L.slamgpu_stat(self._h, 4))
 
     def comm_init(self, rank, world, unique_id):
         buf = (C.c_char * 128).from_buffer_copy(bytes(unique_id))

@@ -106,7 +106,7 @@ static void free_all(slamgpu *h) {
         if (e) cudaEventDestroy(e);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     void *dev[] = {h->pose[0], h->pose[1], h->w, h->lm_mean, h->lm_cov, h->gauss, h->unif_base, h->di_base, h->cdf,
-                   h->mloc, h->sel, h->keep, h->tot_w, h->tot_c, h->tot_s, h->bmax, h->d_sc, h->d_z,
+                   h->mloc, h->sel, h->keep, h->tot_slab, h->xflags, h->d_sc, h->d_z,
                    h->d_rec_in, h->d_rec_out, h->d_est, h->keeplog, h->anc, h->d_phys, h->fb_list, h->fb_count};
     for (void *p : dev)
         if (p) cudaFree(p);
@@ -122,8 +122,7 @@ static int setup_global(slamgpu *h) {
     const size_t Pg = h->Pg;
     h->nb = (h->P + SLAM_SCAN_BLOCK - 1) / SLAM_SCAN_BLOCK;
     h->nbg = (Pg + SLAM_SCAN_BLOCK - 1) / SLAM_SCAN_BLOCK;
-    void **bufs[] = {(void **) &h->cdf, (void **) &h->mloc, (void **) &h->tot_w, (void **) &h->tot_c,
-                     (void **) &h->tot_s, (void **) &h->bmax};
+    void **bufs[] = {(void **) &h->cdf, (void **) &h->mloc, (void **) &h->tot_slab, (void **) &h->xflags};
     for (void **b : bufs)
         if (*b) {
             cudaFree(*b);
@@ -131,10 +130,13 @@ static int setup_global(slamgpu *h) {
         }
     CU(cudaMalloc(&h->cdf, sizeof(float) * Pg));
     CU(cudaMalloc(&h->mloc, sizeof(float) * Pg));
-    CU(cudaMalloc(&h->tot_w, sizeof(float) * h->nbg));
-    CU(cudaMalloc(&h->tot_c, sizeof(float) * h->nbg));
-    CU(cudaMalloc(&h->tot_s, sizeof(float) * h->nbg));
-    CU(cudaMalloc(&h->bmax, sizeof(float) * h->nbg));
+    CU(cudaMalloc(&h->tot_slab, sizeof(float) * 4 * h->nbg));
+    h->tot_w = h->tot_slab;
+    h->tot_c = h->tot_slab + h->nbg;
+    h->tot_s = h->tot_slab + 2 * h->nbg;
+    h->bmax = h->tot_slab + 3 * h->nbg;
+    CU(cudaMalloc(&h->xflags, sizeof(unsigned long long) * SLAM_MAX_RANKS));
+    CU(cudaMemset(h->xflags, 0, sizeof(unsigned long long) * SLAM_MAX_RANKS));
     if (h->keeplog) {
         cudaFree(h->keeplog);
         h->keeplog = nullptr;
@@ -177,7 +179,9 @@ static int create_impl(const slamgpu_config *cfg, slamgpu *h) {
     CU(cudaMalloc(&h->sel, sizeof(float) * P));
     CU(cudaMalloc(&h->keep, sizeof(int) * P));
     CU(cudaMalloc(&h->d_sc, sizeof(Scalars)));
+    CU(cudaMemset(h->d_sc, 0, sizeof(Scalars)));
     CU(cudaHostAlloc(&h->h_sc, sizeof(Scalars), cudaHostAllocDefault));
+    memset(h->h_sc, 0, sizeof(Scalars));
     h->est_blocks = 148 * 4;
     CU(cudaMalloc(&h->d_est, sizeof(EstPartial) * (h->est_blocks + 1)));
     CU(cudaHostAlloc(&h->h_est, sizeof(EstPartial), cudaHostAllocDefault));
@@ -260,6 +264,11 @@ extern "C" int64_t slamgpu_stat(slamgpu_t *h, int32_t which) {
         case SLAMGPU_STAT_RESAMPLES: return h->stat_resamples;
         case SLAMGPU_STAT_CHAIN_STEPS: return h->stat_chain_steps;
         case SLAMGPU_STAT_ROWS_FUSED: return h->stat_rows_fused;
+        case SLAMGPU_STAT_REMOTE_SOURCES: {  // as of the last weights read-back (lags the newest resample by one)
+            unsigned long long v;
+            memcpy(&v, &h->h_sc->pad[1], sizeof(v));
+            return (int64_t) v;
+        }
     }
     return 0;
 }
@@ -301,8 +310,31 @@ static int flush_predicts(slamgpu *h) {
 }
 
 // ---- landmark row pool: deferred resampling of the maps (kernels.cuh K7) ---------------------------------------
+// Chunk stride of spread_block() for a grid of nblocks CTAs of `threads` slots (0 = launch order, when the grid does not
+// split into whole chunks): about 0.618 x the chunk count, made coprime to it.
+static unsigned spread_stride(unsigned nblocks, unsigned threads) {
+    const unsigned per = SLAM_SPREAD_CHUNK_SLOTS / threads;
+    if (nblocks % per != 0 || nblocks / per < 8) return 0;
+    const unsigned nch = nblocks / per;
+    unsigned s = (unsigned) (nch * 0.6180339887) | 1u;
+    auto gcd = [](unsigned a, unsigned b) {
+        while (b) {
+            const unsigned t = a % b;
+            a = b;
+            b = t;
+        }
+        return a;
+    };
+    while (gcd(s, nch) != 1) s += 2;
+    return s % nch;
+}
+
 static int peer_maps(slamgpu *h, PeerMaps *pm) {
-    if (h->world > 1) return comm_peer_maps(h->comm, h, pm);
+    if (h->world > 1) {
+        RET(comm_peer_maps(h->comm, h, pm));
+        pm->spread = spread_stride(grid_for(h->P, 256), 256);
+        return SLAMGPU_OK;
+    }
     memset(pm, 0, sizeof(*pm));
     pm->world = 1;
     pm->pose[0][0] = h->pose[0];
@@ -368,7 +400,7 @@ static int materialise(slamgpu *h, const std::vector<int> &want) {
                 h->row_epoch[l] = h->epoch;
             }
             // sharded: a destination row was a source of an earlier chunk; no rank may overwrite it while a peer reads
-            if (h->world > 1) RET(comm_barrier(h->comm, h->stream));
+            if (h->world > 1) RET(comm_exchange(h->comm, h, nullptr, 0, false));
             dim3 grid(grid_for(P, 256), (n + SLAM_GATHER_ROWS - 1) / SLAM_GATHER_ROWS);
             k_materialise_rows<<<grid, 256, 0, h->stream>>>(pm, h->ring(), P, anc_ptr, (long long) Pg, mv, n);
             KCHECK();
@@ -631,6 +663,17 @@ static int plan_fused_remap(slamgpu *h, const int *idf, int K, std::vector<int> 
     }
     h->stat_rows_moved += n_stale;
     h->stat_rows_fused += n_stale;
+    if (getenv("SLAMGPU_DIAG")) {  // lineage statistics of the ancestor map about to be used (debug aid, synchronises)
+        unsigned long long *d_cnt, h_cnt[2];
+        CU(cudaMalloc(&d_cnt, 16));
+        CU(cudaMemsetAsync(d_cnt, 0, 16, h->stream));
+        k_diag_ancestors<<<grid_for(h->P, 256), 256, 0, h->stream>>>(*anc, h->P, (long long) h->slot0, d_cnt);
+        CU(cudaMemcpyAsync(h_cnt, d_cnt, 16, cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+        cudaFree(d_cnt);
+        fprintf(stderr, "[slamgpu diag] rank %d epoch %lld lag %lld rows %d remote %.4f distinct %.4f\n", h->rank,
+                h->epoch, h->epoch - e, n_stale, (double) h_cnt[0] / h->P, (double) h_cnt[1] / h->P);
+    }
     return SLAMGPU_OK;
 }
 
@@ -704,7 +747,8 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
                     pr.cov[r] = pm.cov[r];
                 }
                 pr.world = h->world;
-                RET(comm_barrier(h->comm, h->stream));
+                pr.spread = spread_stride(grid, SLAM_UPDATE_THREADS);
+                RET(comm_exchange(h->comm, h, nullptr, 0, false));
             }
             const long long Pgl = (long long) h->Pg;
             if (anc) {
@@ -772,7 +816,7 @@ static int resample_indices(slamgpu *h) {
     const float k = (float) (1.0 / (float) Pg);
     const float khalf = k / 2;
     Scalars *d = h->d_sc;
-    CU(cudaMemsetAsync(&d->anomaly, 0, sizeof(int), h->stream));
+    CU(cudaMemsetAsync(&d->anomaly, 0, 2 * sizeof(int), h->stream));  // anomaly and pad[0] = exchange error
     if (h->cfg.scan_mode == SLAMGPU_SCAN_REFERENCE) {
         if (h->world > 1) return slam_fail(SLAMGPU_EINVAL, "SLAMGPU_SCAN_REFERENCE is a one-device order");
         k_reference_weights<<<1, 1, 0, h->stream>>>(h->w, P, h->di(), h->unif(), k, khalf, h->mloc, h->cdf, h->sel,
@@ -790,7 +834,10 @@ static int resample_indices(slamgpu *h) {
     k_block_totals<<<nb, SLAM_SCAN_BLOCK, 0, h->stream>>>(h->w, P, h->tot_w + b0);
     KCHECK();
     LAUNCHED(h, SLAMGPU_T_WEIGHTS);
-    if (h->world > 1) RET(comm_allgather_f32(h->comm, h->tot_w, h->nb, h->stream));
+    if (h->world > 1) {
+        const int arr[1] = {0};
+        RET(comm_exchange(h->comm, h, arr, 1, false));
+    }
     // B: recursive levels -> ws
     RET(launch_upper(h, h->tot_w, &d->ws, nullptr, nullptr, (int) h->nbg, 0));
     // C: normalise, local cdf scan, totals
@@ -799,10 +846,8 @@ static int resample_indices(slamgpu *h) {
     KCHECK();
     LAUNCHED(h, SLAMGPU_T_WEIGHTS);
     if (h->world > 1) {
-        RET(comm_group_begin(h->comm));
-        RET(comm_allgather_f32(h->comm, h->tot_c, h->nb, h->stream));
-        RET(comm_allgather_f32(h->comm, h->tot_s, h->nb, h->stream));
-        RET(comm_group_end(h->comm));
+        const int arr[2] = {1, 2};
+        RET(comm_exchange(h->comm, h, arr, 2, false));
     }
     // D: recursive levels of both -> csum, s2
     RET(launch_upper(h, h->tot_c, &d->csum, h->tot_s, &d->s2, (int) h->nbg, 0));
@@ -821,10 +866,8 @@ static int resample_indices(slamgpu *h) {
         // peer mappings.  This exchange is also the stream-ordered barrier that makes every rank's k_cdf_finalise
         // visible before any rank searches (and the next update's first exchange keeps a rank from overwriting its
         // CDF while a peer still searches it).
-        RET(comm_group_begin(h->comm));
-        RET(comm_allgather_f32(h->comm, h->bmax, h->nb, h->stream));
-        RET(comm_halo_unif(h->comm, h->unif_base, P, h->stream));
-        RET(comm_group_end(h->comm));
+        const int arr[1] = {3};
+        RET(comm_exchange(h->comm, h, arr, 1, true));
     }
     RET(launch_upper(h, h->bmax, nullptr, nullptr, nullptr, (int) h->nbg, 1));
     // F: select + search
@@ -867,9 +910,10 @@ static int resample_state(slamgpu *h) {
     RET(peer_maps(h, &pm));
     // sharded: every rank's update kernels must be done before a peer reads its poses, and the buffer written here
     // was the source of the previous resample
-    if (h->world > 1) RET(comm_barrier(h->comm, h->stream));
+    if (h->world > 1) RET(comm_exchange(h->comm, h, nullptr, 0, false));
     k_gather_pose<<<grid_for(P, 256), 256, 0, h->stream>>>(pm, h->cur, h->pose[h->cur ^ 1], h->w, h->keep, P,
-                                                           (long long) Pg, new_w);
+                                                           (long long) Pg, new_w, h->rank,
+                                                           (unsigned long long *) &h->d_sc->pad[1]);
     KCHECK();
     LAUNCHED(h, SLAMGPU_T_GATHER);
     h->cur ^= 1;
@@ -905,6 +949,7 @@ extern "C" int slamgpu_resample(slamgpu_t *h, const double *unif, int32_t *keep_
     CU(cudaMemcpyAsync(h->h_sc, h->d_sc, sizeof(Scalars), cudaMemcpyDeviceToHost, h->stream));
     RET(span_end(h, &sp));
     CU(cudaStreamSynchronize(h->stream));
+    if (h->h_sc->pad[0]) return slam_fail(SLAMGPU_ECOMM, "a peer device never arrived at an exchange (sharded resample)");
     if (h->h_sc->anomaly) {
         // knife-edge ordering the search could not prove: run the exact sequential merge (core.cpp:800-806)
         if (h->world > 1) return slam_fail(SLAMGPU_ECOMM, "sequential keep[] fallback is not available when sharded");

@@ -9,6 +9,7 @@
 #include <dlfcn.h>
 #include <nccl.h>
 
+#include <cstdlib>
 #include <cstring>
 
 #include "handle.h"
@@ -56,7 +57,8 @@ struct SlamComm {
     ncclComm_t comm = nullptr;
     bool peers_open = false;
     PeerMaps peers;
-    void *opened[SLAM_MAX_RANKS][6];
+    void *opened[SLAM_MAX_RANKS][9];
+    unsigned long long epoch = 0;  // exchanges issued so far (k_xchg arrival counter)
     unsigned char *d_small = nullptr;  // scratch for handle exchange, barriers, estimate
     unsigned char *h_small = nullptr;
 };
@@ -101,7 +103,7 @@ SlamComm *comm_create(int rank, int world, const void *id128, int device, std::s
         delete c;
         return nullptr;
     }
-    if (cudaMalloc(&c->d_small, 4096) != cudaSuccess || cudaHostAlloc(&c->h_small, 4096, cudaHostAllocDefault) != cudaSuccess) {
+    if (cudaMalloc(&c->d_small, 8192) != cudaSuccess || cudaHostAlloc(&c->h_small, 8192, cudaHostAllocDefault) != cudaSuccess) {
         *err = "comm scratch allocation failed";
         g_nccl.CommDestroy(c->comm);
         delete c;
@@ -113,7 +115,7 @@ SlamComm *comm_create(int rank, int world, const void *id128, int device, std::s
 void comm_destroy(SlamComm *c) {
     if (!c) return;
     for (int r = 0; r < c->world; r++)
-        for (int j = 0; j < 6; j++)
+        for (int j = 0; j < 9; j++)
             if (c->opened[r][j]) cudaIpcCloseMemHandle(c->opened[r][j]);
     if (c->comm) g_nccl.CommDestroy(c->comm);
     if (c->d_small) cudaFree(c->d_small);
@@ -136,30 +138,30 @@ int comm_halo_unif(SlamComm *c, double *unif_base, size_t P, cudaStream_t st) {
 
 static int barrier(SlamComm *c, cudaStream_t st) {
     // stream-ordered: completes on a rank only once every rank's stream has reached it
-    float *b = (float *) (c->d_small + 2048);
+    float *b = (float *) (c->d_small + 6144);
     NC(g_nccl.AllGather(b + c->rank, b, 1, ncclFloat32, c->comm, st));
     return SLAMGPU_OK;
 }
 
 static int open_peers(SlamComm *c, slamgpu *h) {
     if (c->peers_open) return SLAMGPU_OK;
-    cudaIpcMemHandle_t mine[6];
-    void *ptrs[6] = {h->pose[0], h->pose[1], h->lm_mean, h->lm_cov, h->cdf, h->mloc};
-    for (int j = 0; j < 6; j++) CU(cudaIpcGetMemHandle(&mine[j], ptrs[j]));
+    cudaIpcMemHandle_t mine[9];
+    void *ptrs[9] = {h->pose[0], h->pose[1], h->lm_mean, h->lm_cov, h->cdf, h->mloc, h->tot_slab, h->xflags, h->unif_base};
+    for (int j = 0; j < 9; j++) CU(cudaIpcGetMemHandle(&mine[j], ptrs[j]));
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is 64 bytes");
-    const size_t per = sizeof(mine);  // 384 B per rank
+    const size_t per = sizeof(mine);  // 576 B per rank
     CU(cudaMemcpyAsync(c->d_small + (size_t) c->rank * per, mine, per, cudaMemcpyHostToDevice, h->stream));
     NC(g_nccl.AllGather(c->d_small + (size_t) c->rank * per, c->d_small, per, ncclChar, c->comm, h->stream));
     CU(cudaMemcpyAsync(c->h_small, c->d_small, per * c->world, cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     for (int r = 0; r < c->world; r++) {
-        void *p[6];
+        void *p[9];
         if (r == c->rank) {
-            for (int j = 0; j < 6; j++) p[j] = ptrs[j];
+            for (int j = 0; j < 9; j++) p[j] = ptrs[j];
         } else {
-            cudaIpcMemHandle_t hd[6];
+            cudaIpcMemHandle_t hd[9];
             memcpy(hd, c->h_small + (size_t) r * per, per);
-            for (int j = 0; j < 6; j++) {
+            for (int j = 0; j < 9; j++) {
                 CU(cudaIpcOpenMemHandle(&p[j], hd[j], cudaIpcMemLazyEnablePeerAccess));
                 c->opened[r][j] = p[j];
             }
@@ -170,6 +172,9 @@ static int open_peers(SlamComm *c, slamgpu *h) {
         c->peers.cov[r] = (const float4 *) p[3];
         c->peers.cdf[r] = (const float *) p[4];
         c->peers.mloc[r] = (const float *) p[5];
+        c->peers.slab[r] = (float *) p[6];
+        c->peers.flags[r] = (unsigned long long *) p[7];
+        c->peers.unif[r] = (double *) p[8];
     }
     c->peers.world = c->world;
     c->peers_open = true;
@@ -183,6 +188,87 @@ int comm_peer_maps(SlamComm *c, slamgpu *h, PeerMaps *out) {
 }
 
 int comm_barrier(SlamComm *c, cudaStream_t st) { return barrier(c, st); }
+
+// ---- small exchanges over peer memory --------------------------------------------------------------------------------
+// The sharded resample needs three tiny all-gathers (<= 4 KB per rank) and a few barriers per update.  Through NCCL each
+// costs a launch plus ~20 us of protocol at 8 devices; here one 1-CTA kernel per rank STORES its chunk straight into
+// every peer's copy of the array over NVLink (the buffers are CUDA-IPC mapped), publishes an arrival counter in every
+// peer's flag array with a system-scope fence, and spins on its own flags until all peers have arrived: the stores of a
+// peer are visible once its counter is.  Every rank issues the same sequence of exchanges, so the counter is simply the
+// exchange number.  A chunk is rewritten only after at least one later exchange (= barrier) that follows its last
+// reader in stream order, see capi.cu resample_indices.  The wait is bounded (~20 s of SM clocks): a missing peer
+// raises *error, which the host turns into SLAMGPU_ECOMM, instead of hanging the device.
+__global__ void __launch_bounds__(256) k_xchg(const XchgArgs a) {
+    const int tid = threadIdx.x;
+    for (int k = 0; k < a.narr; k++) {
+        const float *src = a.slab[a.rank] + a.arr_off[k] + a.b0;
+        for (int r = 0; r < a.world; r++) {
+            if (r == a.rank) continue;
+            float *dst = a.slab[r] + a.arr_off[k] + a.b0;
+            for (int i = tid; i < a.count; i += blockDim.x) dst[i] = src[i];
+        }
+    }
+    if (a.halo && a.rank + 1 < a.world && tid < 2)  // the next rank's search needs this rank's last two uniforms
+        a.unif[a.rank + 1][tid] = a.unif[a.rank][a.P + tid];
+    __threadfence_system();
+    __syncthreads();
+    if (tid < a.world) {
+        __threadfence_system();  // cumulative: the whole CTA's stores (ordered by the barrier) precede the counter
+        volatile unsigned long long *theirs = a.flags[tid] + a.rank;
+        *theirs = a.epoch;
+        volatile unsigned long long *mine = a.flags[a.rank] + tid;
+        const long long t0 = clock64();
+        while (*mine < a.epoch) {
+            if (clock64() - t0 > 40000000000ll) {
+                *a.error = 1;
+                break;
+            }
+        }
+    }
+    __threadfence_system();
+    __syncthreads();
+}
+
+int comm_exchange(SlamComm *c, slamgpu *h, const int *arrays, int narr, bool halo) {
+    RET(open_peers(c, h));
+    static const bool via_nccl = getenv("SLAMGPU_XCHG_NCCL") != nullptr;  // A/B switch: the same exchanges through NCCL
+    if (via_nccl) {
+        if (narr == 0 && !halo) return barrier(c, h->stream);
+        NC(g_nccl.GroupStart());
+        for (int k = 0; k < narr; k++) {
+            float *buf = h->tot_slab + (size_t) arrays[k] * h->nbg;
+            NC(g_nccl.AllGather(buf + (size_t) c->rank * h->nb, buf, h->nb, ncclFloat32, c->comm, h->stream));
+        }
+        if (halo) {
+            if (c->rank + 1 < c->world)
+                NC(g_nccl.Send(h->unif_base + h->P, 2, ncclFloat64, c->rank + 1, c->comm, h->stream));
+            if (c->rank > 0) NC(g_nccl.Recv(h->unif_base, 2, ncclFloat64, c->rank - 1, c->comm, h->stream));
+        }
+        NC(g_nccl.GroupEnd());
+        return SLAMGPU_OK;
+    }
+    XchgArgs a;
+    memset(&a, 0, sizeof(a));
+    for (int r = 0; r < c->world; r++) {
+        a.slab[r] = c->peers.slab[r];
+        a.flags[r] = c->peers.flags[r];
+        a.unif[r] = c->peers.unif[r];
+    }
+    a.rank = c->rank;
+    a.world = c->world;
+    a.epoch = ++c->epoch;
+    a.narr = narr;
+    for (int k = 0; k < narr; k++) a.arr_off[k] = arrays[k] * (int) h->nbg;
+    a.b0 = (int) (h->slot0 / SLAM_SCAN_BLOCK);
+    a.count = (int) h->nb;
+    a.halo = halo ? 1 : 0;
+    a.P = h->P;
+    a.error = &h->d_sc->pad[0];
+    k_xchg<<<1, 256, 0, h->stream>>>(a);
+    if (cudaGetLastError() != cudaSuccess) return slam_fail(SLAMGPU_ECOMM, "peer-memory exchange launch failed");
+    h->launches++;
+    return SLAMGPU_OK;
+}
 
 // Consecutive small exchanges issued between these two calls go out as ONE NCCL launch.
 int comm_group_begin(SlamComm *c) {

@@ -76,7 +76,9 @@ struct slamgpu {
     float *cdf = nullptr, *mloc = nullptr;  // [Pg]
     float *sel = nullptr;        // [P]
     int *keep = nullptr;         // [P]
-    float *tot_w = nullptr, *tot_c = nullptr, *tot_s = nullptr, *bmax = nullptr;  // [nb_global]
+    float *tot_slab = nullptr;   // [4][nb_global]: the four arrays below, one allocation (one peer mapping)
+    float *tot_w = nullptr, *tot_c = nullptr, *tot_s = nullptr, *bmax = nullptr;  // [nb_global] each
+    unsigned long long *xflags = nullptr;  // [SLAM_MAX_RANKS] arrival counters written by the peers (comm.cu k_xchg)
     size_t nb = 0, nbg = 0;      // local / global 1024-blocks
     Scalars *d_sc = nullptr, *h_sc = nullptr;
     float2 *d_z = nullptr;       // staged observation set: [K] z | [K] row | [K] row_dst (capi.cu stage_obs_host)
@@ -136,6 +138,10 @@ int comm_halo_unif(SlamComm *c, double *unif_base, size_t P, cudaStream_t st);
 int comm_peer_maps(SlamComm *c, slamgpu *h, PeerMaps *out);
 // Stream-ordered barrier over all ranks (nobody passes until every rank's stream has reached it).
 int comm_barrier(SlamComm *c, cudaStream_t st);
+// Small exchange over peer memory instead of NCCL (latency: one 1-CTA kernel): all-gathers this rank's chunk
+// [b0, b0 + nb) of the listed block-total arrays (0 tot_w, 1 tot_c, 2 tot_s, 3 bmax), optionally sends the uniform
+// halo to the next rank, and is a stream-ordered barrier over all ranks.  narr == 0: barrier only.
+int comm_exchange(SlamComm *c, slamgpu *h, const int *arrays, int narr, bool halo);
 int comm_group_begin(SlamComm *c);
 int comm_group_end(SlamComm *c);
 int comm_allgather_i32(SlamComm *c, int *buf, size_t count, cudaStream_t st);

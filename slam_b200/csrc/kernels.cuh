@@ -279,6 +279,18 @@ __device__ __forceinline__ void remap_source(const PeerRows &pr, long long q, si
     scov = pr.cov[r] + ql;
 }
 
+// Sharded resampling pulls particles across the shard edges, so the slots whose ancestor column lives on a peer sit
+// together at one end of the shard: in launch order their CTAs would run together, NVLink-bound, as the kernel's tail
+// (N=8: the update kernel of the worst rank took ~2.5x its HBM-bound time).  spread_block() walks the grid in chunks of
+// SLAM_SPREAD_CHUNK_SLOTS consecutive slots with a stride coprime to the chunk count, so peer reads are interleaved
+// with local, HBM-bound CTAs for the whole kernel and hide behind them; a chunk stays contiguous (DRAM pages).
+#define SLAM_SPREAD_CHUNK_SLOTS 2048
+__device__ __forceinline__ unsigned spread_block(unsigned b, unsigned nblocks, unsigned stride, unsigned per_chunk) {
+    if (stride == 0) return b;
+    const unsigned nch = nblocks / per_chunk, c = b / per_chunk;
+    return (unsigned) (((unsigned long long) c * stride) % nch) * per_chunk + (b % per_chunk);
+}
+
 template <bool REMAP>
 __global__ void __launch_bounds__(128) k_fs2_update_listed(PoseSoA s, MapRing m, size_t P, ObsSet o, int K, float4 Rm,
                                                            const float *__restrict__ gauss,
@@ -326,7 +338,7 @@ __device__ __forceinline__ void cp_async_wait() {
 // WRITTEN to column p of a fresh physical row, so the row needs no separate k_materialise_rows pass (one read + one
 // write of 24 B per particle-landmark saved on every update that follows a resample).
 template <bool REMAP>
-__global__ void __launch_bounds__(SLAM_UPDATE_THREADS) k_fs2_update_fast(PoseSoA s, MapRing m, size_t P, ObsSet o, int K,
+__global__ void __launch_bounds__(SLAM_UPDATE_THREADS, 7) k_fs2_update_fast(PoseSoA s, MapRing m, size_t P, ObsSet o, int K,
                                                                          float4 Rm, const float *__restrict__ gauss,
                                                                          const int *__restrict__ anc, PeerRows pr,
                                                                          long long n_global,
@@ -337,7 +349,8 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS) k_fs2_update_fast(PoseSoA
     float2 *sz;
     unsigned long long *soff, *doff;
     stage_obs_fs2<REMAP>(slam_smem + (sizeof(float4) + sizeof(float2)) * D * T, o, K, P, sz, soff, doff);
-    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned blk = REMAP ? spread_block(blockIdx.x, gridDim.x, pr.spread, SLAM_SPREAD_CHUNK_SLOTS / T) : blockIdx.x;
+    const size_t p = (size_t) blk * blockDim.x + threadIdx.x;
     if (p >= P) return;
     const float2 *const mean_p = m.mean + p;
     const float4 *const cov_p = m.cov + p;
@@ -883,17 +896,43 @@ __global__ void k_neff(const float *__restrict__ s2, float *__restrict__ neff_ou
 // ---------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_gather_pose(PeerMaps pm, int cur, float *__restrict__ dst_pose,
                                                      float *__restrict__ w, const int *__restrict__ keep, size_t P,
-                                                     long long n_global, float new_w) {
+                                                     long long n_global, float new_w, int rank,
+                                                     unsigned long long *__restrict__ remote_sources) {
     const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= P) return;
-    long long k = keep[p];
-    if (k < 0) k = n_global - 1;
-    const int r = (pm.world > 1) ? (int) (k / (long long) P) : 0;
-    const size_t sidx = (size_t) (k - (long long) r * (long long) P);
-    const float *src = pm.pose[cur][r];
+    int remote = 0;
+    if (p < P) {
+        long long k = keep[p];
+        if (k < 0) k = n_global - 1;
+        const int r = (pm.world > 1) ? (int) (k / (long long) P) : 0;
+        const size_t sidx = (size_t) (k - (long long) r * (long long) P);
+        const float *src = pm.pose[cur][r];
 #pragma unroll
-    for (int c = 0; c < 12; c++) dst_pose[c * P + p] = src[c * P + sidx];
-    w[p] = new_w;
+        for (int c = 0; c < 12; c++) dst_pose[c * P + p] = src[c * P + sidx];
+        w[p] = new_w;
+        remote = (pm.world > 1 && r != rank);
+    }
+    if (pm.world > 1) {  // SLAMGPU_STAT_REMOTE_SOURCES: how many slots took their particle from another device
+        const int n = __syncthreads_count(remote);
+        if (threadIdx.x == 0 && n) atomicAdd(remote_sources, (unsigned long long) n);
+    }
+}
+
+// SLAMGPU_DIAG: out[0] += slots whose ancestor lives outside [slot0, slot0 + P); out[1] += slots whose ancestor differs
+// from the previous slot's (= distinct ancestors, the map being non-decreasing).
+__global__ void __launch_bounds__(256) k_diag_ancestors(const int *__restrict__ anc, size_t P, long long slot0,
+                                                        unsigned long long *__restrict__ out) {
+    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    int remote = 0, fresh = 0;
+    if (p < P) {
+        const long long a = anc[p];
+        remote = a >= 0 && (a < slot0 || a >= slot0 + (long long) P);
+        fresh = p == 0 || anc[p - 1] != anc[p];
+    }
+    const int nr = __syncthreads_count(remote), nf = __syncthreads_count(fresh);
+    if (threadIdx.x == 0) {
+        if (nr) atomicAdd(out, (unsigned long long) nr);
+        if (nf) atomicAdd(out + 1, (unsigned long long) nf);
+    }
 }
 
 // anc[p] <- keep_{e_to}[ ... keep_{e_from}[ start ] ... ] for e = e_from down to e_to, where start = anc[p] (continuing
@@ -918,7 +957,8 @@ __global__ void __launch_bounds__(256) k_chain(int *__restrict__ anc, size_t P, 
 __global__ void __launch_bounds__(256) k_materialise_rows(PeerMaps pm, MapRing m, size_t P,
                                                           const int *__restrict__ anc, long long n_global,
                                                           const RowMoves mv, int nrows) {
-    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t p = (size_t) spread_block(blockIdx.x, gridDim.x, pm.spread, SLAM_SPREAD_CHUNK_SLOTS / 256) * blockDim.x +
+                     threadIdx.x;
     if (p >= P) return;
     long long k = anc[p];
     if (k < 0) k = n_global - 1;

@@ -27,13 +27,33 @@ struct PeerMaps {  // this device's and (when sharded) the peers' buffers, index
     const float4 *cov[SLAM_MAX_RANKS];
     const float *cdf[SLAM_MAX_RANKS];   // each rank's [Pg]-indexed CDF / running-maximum buffers (its own block filled)
     const float *mloc[SLAM_MAX_RANKS];
+    float *slab[SLAM_MAX_RANKS];               // block-total arrays [4][nbg]: tot_w | tot_c | tot_s | bmax
+    unsigned long long *flags[SLAM_MAX_RANKS]; // [SLAM_MAX_RANKS] arrival counters of the peer-memory exchange
+    double *unif[SLAM_MAX_RANKS];              // unif_base (2-slot halo in front)
     int world;
+    unsigned spread;  // see PeerRows
+};
+
+// One small exchange over peer memory (comm.cu k_xchg): every rank pushes its chunk of up to 3 block-total arrays into
+// every peer's copy, optionally its last two resample uniforms into the next rank's halo, then signals and waits.
+struct XchgArgs {
+    float *slab[SLAM_MAX_RANKS];
+    unsigned long long *flags[SLAM_MAX_RANKS];
+    double *unif[SLAM_MAX_RANKS];
+    int rank, world;
+    unsigned long long epoch;
+    int narr, arr_off[3];  // element offsets of the arrays inside the slab
+    int b0, count;         // this rank's chunk
+    int halo;
+    unsigned long long P;
+    int *error;            // set when a peer never arrived
 };
 
 struct PeerRows {  // landmark pools by rank, for kernels that read a particle's ancestor column wherever it lives
     const float2 *mean[SLAM_MAX_RANKS];
     const float4 *cov[SLAM_MAX_RANKS];
     int world;
+    unsigned spread;  // 0, or the chunk stride of spread_block(): remote-heavy CTAs interleaved with local ones
 };
 
 struct RowPair {  // one row move of a materialisation: physical source row -> physical destination row
