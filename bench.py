@@ -345,6 +345,10 @@ def run_ours(a):
     remote_frac = max_over_ranks(remote / max(1, n_resamples * P)) if world > 1 else 0.0
     fam = f.timing_read()
     f.timing_enable(False)
+    if os.environ.get("SLAM_BENCH_RANK_REPORT"):  # per-rank family times (the JSON line carries rank 0's)
+        print("[rank %d] ms/step by family: %s  remote sources/resample: %.3f"
+              % (rank, {k: round(v["ms"] / a.steps, 4) for k, v in fam.items()}, remote / max(1, n_resamples * P)),
+              file=sys.stderr, flush=True)
     resample_rate = state["resamples"] / max(1, state["steps"])
 
     # ---- end-to-end leg: host buffers in, result out, every step ---------------------------------------------

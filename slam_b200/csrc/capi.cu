@@ -94,6 +94,7 @@ extern "C" void slamgpu_host_free(void *p) {
 static void free_all(slamgpu *h) {
     if (!h) return;
     cudaSetDevice(h->cfg.device);
+    if (h->log_stream) cudaStreamSynchronize(h->log_stream);  // an all-gather of the keep log may still be in flight
     if (h->comm) comm_destroy(h->comm);
     for (auto &sp : h->spans) {
         cudaEventDestroy(sp.a);
@@ -102,9 +103,10 @@ static void free_all(slamgpu *h) {
     for (auto e : h->free_events) cudaEventDestroy(e);
     for (auto e : h->obs_ev)
         if (e) cudaEventDestroy(e);
-    for (auto e : {h->ev_in, h->ev_gauss, h->ev_unif})
+    for (auto e : {h->ev_in, h->ev_gauss, h->ev_unif, h->ev_keep, h->ev_log})
         if (e) cudaEventDestroy(e);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+    if (h->log_stream) cudaStreamDestroy(h->log_stream);
     void *dev[] = {h->pose[0], h->pose[1], h->w, h->lm_mean, h->lm_cov, h->gauss, h->unif_base, h->di_base, h->cdf,
                    h->mloc, h->sel, h->keep, h->tot_slab, h->xflags, h->d_sc, h->d_z,
                    h->d_rec_in, h->d_rec_out, h->d_est, h->keeplog, h->anc, h->d_phys, h->fb_list, h->fb_count};
@@ -901,11 +903,29 @@ static int resample_state(slamgpu *h) {
     const float new_w = 1.0f / (float) Pg;
     TimedSpan sg;
     RET(span_begin(h, SLAMGPU_T_GATHER, &sg));
+    if (h->log_pending) {  // the previous epoch's log must be whole before ancestor chains step through it
+        CU(cudaStreamWaitEvent(h->stream, h->ev_log, 0));
+        h->log_pending = false;
+    }
     h->epoch++;
     h->stat_resamples++;
     int *slot = h->keeplog + (size_t) (h->epoch % h->H) * Pg;
     CU(cudaMemcpyAsync(slot + h->slot0, h->keep, sizeof(int) * P, cudaMemcpyDeviceToDevice, h->stream));
-    if (h->world > 1) RET(comm_allgather_i32(h->comm, slot, P, h->stream));
+    if (h->world > 1) {
+        // The peers' parts of this epoch's keep[] are only read by ancestor chains that START at a later epoch (a
+        // chain's first step looks up its own slot, i.e. this device's part): the all-gather runs on its own stream
+        // behind the coming predict / update and is waited for at the next resample.
+        if (!h->log_stream) {
+            CU(cudaStreamCreateWithFlags(&h->log_stream, cudaStreamNonBlocking));
+            CU(cudaEventCreateWithFlags(&h->ev_keep, cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&h->ev_log, cudaEventDisableTiming));
+        }
+        CU(cudaEventRecord(h->ev_keep, h->stream));
+        CU(cudaStreamWaitEvent(h->log_stream, h->ev_keep, 0));
+        RET(comm_allgather_i32(h->comm, slot, P, h->log_stream));
+        CU(cudaEventRecord(h->ev_log, h->log_stream));
+        h->log_pending = true;
+    }
     PeerMaps pm;
     RET(peer_maps(h, &pm));
     // sharded: every rank's update kernels must be done before a peer reads its poses, and the buffer written here

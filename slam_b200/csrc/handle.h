@@ -94,6 +94,10 @@ struct slamgpu {
     // slamgpu_update's host noise travels on a second stream (capi.cu)
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev_in = nullptr, ev_gauss = nullptr, ev_unif = nullptr;
+    // sharded: the newest keep[] is all-gathered into the log on its own stream, behind the next predict / update
+    cudaStream_t log_stream = nullptr;
+    cudaEvent_t ev_keep = nullptr, ev_log = nullptr;
+    bool log_pending = false;
     bool gauss_inflight = false, unif_inflight = false;
     int gauss_rows_staged = 0;
     // timing
