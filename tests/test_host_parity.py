@@ -141,3 +141,23 @@ def test_drive_steering_sensor_noise_and_association_bitwise(sides):
         for a, b in zip(*outs):
             assert np.array_equal(np.asarray(a), np.asarray(b)), tick
     assert n_seen > 10
+
+
+def test_config_fixture_carries_the_reference_inputs(sides, tmp_path):
+    """tests/golden/config_traces.npz rebuilds BASELINE configs[0..2]' input files on the GPU box: the rebuilt .mat /
+    .ini must parse (by the reference's own parser and by the host's) to what the reference's files parse to, apart
+    from the recorded fixed seed."""
+    from test_gpu_configs import write_inputs
+    h, r, _, _ = sides
+    g = np.load(os.path.join(HERE, "golden", "config_traces.npz"))
+    for tag, name in (("cfg0", "example_webmap"), ("cfg1", "example_loop1"), ("cfg2", "example_loop902")):
+        d = tmp_path / tag
+        d.mkdir()
+        write_inputs(g, tag, str(d))
+        la, wa = read_map(r, os.path.join(REF_DATA, name + ".mat"))
+        for side in (h, r):
+            lb, wb = read_map(side, str(d / "map.mat"))
+            assert np.array_equal(la, lb) and np.array_equal(wa, wb), (tag, name)
+        seed = [s for s in g[tag + "_ini"] if str(s).startswith("SWITCH_SEED_RANDOM")][0].split("=")[1].strip()
+        want = conf_dump(r, os.path.join(REF_DATA, name + ".ini"), {"SWITCH_SEED_RANDOM": seed})
+        assert conf_dump(h, str(d / "map.ini"), {}) == want and conf_dump(r, str(d / "map.ini"), {}) == want
