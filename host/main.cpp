@@ -8,6 +8,7 @@
 //   -device D       CUDA device ordinal
 //   -plot_stride K  feed every K-th particle to the sink (0 = none)
 //   -scan MODE      reference | blocked   (summation order behind the resampling CDF, include/slamgpu.h)
+//   -math MODE      fast | reference      (per-particle arithmetic: the B200 kernels' own / the Eigen call order)
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -67,6 +68,7 @@ int main(int argc, char **argv) {
     const std::string scan = conf.s("scan");
     // the reference order is one device thread: right for the reference's own particle counts, hopeless at 10^6
     opt.scan_mode = scan == "blocked" ? 1 : (scan == "reference" ? 0 : (conf.NPARTICLES > 20000 ? 1 : 0));
+    opt.math_mode = conf.s("math") == "reference" ? 1 : 0;
     std::unique_ptr<PlotSink> sink;
     if (!conf.s("trace").empty()) {
         sink.reset(make_trace_plot(conf.s("trace")));

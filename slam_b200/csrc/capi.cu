@@ -716,7 +716,7 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
         const bool fast = h->cfg.math_mode == SLAMGPU_MATH_FAST;
         std::vector<int> dst(K), vacated;
         const int *anc = nullptr;
-        if (fs2 && fast) {
+        if (fast) {
             for (int i = 0; i < K; i++) rows[i] = dst[i] = h->phys_row(idf[i]);
             RET(plan_fused_remap(h, idf, K, rows, dst, &anc, vacated));
         } else {
@@ -728,31 +728,30 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
         const size_t smem = (sizeof(float2) + sizeof(int)) * K;
         TimedSpan sp;
         RET(span_begin(h, SLAMGPU_T_UPDATE, &sp));
-        const size_t smem_fast = SLAM_OBS_OFF_SMEM(K);
+        PeerRows pr;
+        memset(&pr, 0, sizeof(pr));
+        pr.world = 1;
+        pr.mean[0] = h->lm_mean;
+        pr.cov[0] = h->lm_cov;
+        const long long Pgl = (long long) h->Pg;
+        if (fast && anc && h->world > 1) {
+            // stale rows are read from the rank that holds the ancestor: every rank's earlier writes must have
+            // landed, and the fresh rows written here must no longer be read by anyone (they were vacated by an
+            // earlier kernel of some rank): one stream-ordered barrier covers both
+            PeerMaps pm;
+            RET(peer_maps(h, &pm));
+            for (int r = 0; r < h->world; r++) {
+                pr.mean[r] = pm.mean[r];
+                pr.cov[r] = pm.cov[r];
+            }
+            pr.world = h->world;
+            pr.spread = spread_stride(grid_for(P, fs2 ? SLAM_UPDATE_THREADS : 256), fs2 ? SLAM_UPDATE_THREADS : 256);
+            RET(comm_exchange(h->comm, h, nullptr, 0, false));
+        }
         if (fs2 && fast) {
             const unsigned grid = grid_for(P, SLAM_UPDATE_THREADS), grid_l = std::min<unsigned>(grid, 148u * 4u);
             const size_t sm_f = SLAM_FS2_FAST_SMEM(K), sm_l = SLAM_OBS_FS2_SMEM(K);
             CU(cudaMemsetAsync(h->fb_count, 0, sizeof(int), h->stream));
-            PeerRows pr;
-            memset(&pr, 0, sizeof(pr));
-            pr.world = 1;
-            pr.mean[0] = h->lm_mean;
-            pr.cov[0] = h->lm_cov;
-            if (anc && h->world > 1) {
-                // stale rows are read from the rank that holds the ancestor: every rank's earlier writes must have
-                // landed, and the fresh rows written here must no longer be read by anyone (they were vacated by an
-                // earlier kernel of some rank): one stream-ordered barrier covers both
-                PeerMaps pm;
-                RET(peer_maps(h, &pm));
-                for (int r = 0; r < h->world; r++) {
-                    pr.mean[r] = pm.mean[r];
-                    pr.cov[r] = pm.cov[r];
-                }
-                pr.world = h->world;
-                pr.spread = spread_stride(grid, SLAM_UPDATE_THREADS);
-                RET(comm_exchange(h->comm, h, nullptr, 0, false));
-            }
-            const long long Pgl = (long long) h->Pg;
             if (anc) {
                 k_fs2_update_fast<true><<<grid, SLAM_UPDATE_THREADS, sm_f, h->stream>>>(
                     h->soa(h->cur), h->ring(), P, o, K, Rm, dg, anc, pr, Pgl, h->fb_list, h->fb_count);
@@ -768,13 +767,18 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
                 k_fs2_update_listed<false><<<grid_l, 128, sm_l, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, dg,
                                                                              nullptr, pr, Pgl, h->fb_list, h->fb_count);
             }
-            for (int v : vacated) h->free_rows.insert(h->free_rows.begin(), v);
         } else if (fs2)
             k_fs2_update<<<grid_for(P, 128), 128, smem, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, dg);
+        else if (fast && anc)
+            k_fs1_update_fast<true><<<grid_for(P, 256), 256, SLAM_OBS_FS2_SMEM(K), h->stream>>>(
+                h->soa(h->cur), h->ring(), P, o, K, Rm, anc, pr, Pgl);
         else if (fast)
-            k_fs1_update_fast<<<grid_for(P, 256), 256, smem_fast, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm);
+            k_fs1_update_fast<false><<<grid_for(P, 256), 256, SLAM_OBS_FS2_SMEM(K), h->stream>>>(
+                h->soa(h->cur), h->ring(), P, o, K, Rm, nullptr, pr, Pgl);
         else
             k_fs1_update<<<grid_for(P, 256), 256, smem, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm);
+        if (fast)
+            for (int v : vacated) h->free_rows.insert(h->free_rows.begin(), v);
         KCHECK();
         LAUNCHED(h, SLAMGPU_T_UPDATE);
         RET(span_end(h, &sp));

@@ -436,32 +436,44 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS, 7) k_fs2_update_fast(Pose
 #undef SLAM_SRC_COV
 }
 
-__global__ void __launch_bounds__(256) k_fs1_update_fast(PoseSoA s, MapRing m, size_t P, ObsSet o, int K, float4 Rm) {
+// REMAP as in k_fs2_update_fast: a stale observed row is read at the ancestor's column (on whichever rank holds it) and
+// written to a fresh physical row, so the re-columning of the observed rows costs no extra pass.
+template <bool REMAP>
+__global__ void __launch_bounds__(256) k_fs1_update_fast(PoseSoA s, MapRing m, size_t P, ObsSet o, int K, float4 Rm,
+                                                         const int *__restrict__ anc, PeerRows pr, long long n_global) {
     float2 *sz;
-    unsigned long long *soff;
-    stage_obs_off(o, K, P, sz, soff);
-    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long *soff, *doff;
+    stage_obs_fs2<REMAP>(slam_smem, o, K, P, sz, soff, doff);
+    const unsigned blk = REMAP ? spread_block(blockIdx.x, gridDim.x, pr.spread, SLAM_SPREAD_CHUNK_SLOTS / 256) : blockIdx.x;
+    const size_t p = (size_t) blk * blockDim.x + threadIdx.x;
     if (p >= P) return;
     const float R[4] = {Rm.x, Rm.y, Rm.z, Rm.w};
     float x[3];
     load_pose(s, P, p, x, nullptr);
     float2 *const mean_p = m.mean + p;
     float4 *const cov_p = m.cov + p;
+    const float2 *smean = mean_p;
+    const float4 *scov = cov_p;
+    if (REMAP) remap_source(pr, remap_column(anc, p, n_global), P, smean, scov);
     float wt = 1.0f;
     float xf[2], Pf[4], nxf[2], nPf[4];
-    unsigned long long off = soff[0];
-    lm_load_at(mean_p + off, cov_p + off, nxf, nPf);
+    {
+        const bool stale = REMAP && soff[0] != doff[0];
+        lm_load_at((stale ? smean : mean_p) + soff[0], (stale ? scov : cov_p) + soff[0], nxf, nPf);
+    }
     for (int i = 0; i < K; i++) {
         xf[0] = nxf[0]; xf[1] = nxf[1];
 #pragma unroll
         for (int j = 0; j < 4; j++) Pf[j] = nPf[j];
-        const unsigned long long noff = soff[i + 1];
-        lm_load_at(mean_p + noff, cov_p + noff, nxf, nPf);
+        const int n = min(i + 1, K - 1);  // the last iteration re-reads its own row (no branch around the prefetch)
+        const unsigned long long noff = soff[n];
+        const bool stale = REMAP && noff != doff[n];
+        lm_load_at((stale ? smean : mean_p) + noff, (stale ? scov : cov_p) + noff, nxf, nPf);
         const float z[2] = {sz[i].x, sz[i].y};
         wt = wt * likelihood_and_feature_update_fast(x, R, xf, Pf, z);
-        __stcs(mean_p + off, make_float2(xf[0], xf[1]));
-        __stcs(cov_p + off, make_float4(Pf[0], Pf[2], Pf[1], Pf[3]));
-        off = noff;
+        const unsigned long long d = doff[i];
+        __stcs(mean_p + d, make_float2(xf[0], xf[1]));
+        __stcs(cov_p + d, make_float4(Pf[0], Pf[2], Pf[1], Pf[3]));
     }
     s.w[p] = s.w[p] * wt;
 }

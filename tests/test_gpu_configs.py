@@ -8,7 +8,7 @@ and is held against the trace of the UNMODIFIED reference program on the same in
 Bars: iteration count, true vehicle path and observation counts bit-identical over the whole run (same steering, same
 rand() consumption, same data association sizes); the estimate within 1e-4 (relative to the map scale; 1e-4 rad) of the
 reference's for the first `follow` iterations — the whole run for EKF1; for the particle filters until the first
-knife-edge resampling decision falls the other way (see tests/test_gpu_host_app.py) — and tracking the true path to the
+knife-edge resampling index falls the other way (see tests/test_gpu_host_app.py) — and tracking the true path to the
 end like the reference does."""
 import os
 import subprocess
@@ -41,9 +41,11 @@ def write_inputs(g, tag, d):
         f.write("\n".join(str(s) for s in g[tag + "_ini"]) + "\n")
 
 
-# follow: iterations over which the estimate must equal the reference's to 1e-4.  Measured on B200: EKF1 all 34418,
-# FASTSLAM1 744, FASTSLAM2 264 (then one resampling decision falls the other way); asserted with margin.
-@pytest.mark.parametrize("tag,follow", [("cfg2", None), ("cfg0", 500), ("cfg1", 200)])
+# follow: iterations over which the estimate must equal the reference's to 1e-4 (position relative to max(1, |pose|),
+# heading absolute).  Measured on B200 (tools/config_follow.py): EKF1 all 34418; FASTSLAM1 688 (85 observation
+# updates); FASTSLAM2 136 (16 updates; the same with -math reference: a 100-particle FastSLAM2 amplifies a 1e-7
+# weight difference into a different resampling index within a few updates).  Asserted with margin.
+@pytest.mark.parametrize("tag,follow", [("cfg2", None), ("cfg0", 600), ("cfg1", 120)])
 def test_config_against_reference_program(exe, tmp_path, tag, follow):
     g = np.load(os.path.join(HERE, "golden", "config_traces.npz"))
     method = str(g[tag + "_method"])
@@ -61,10 +63,10 @@ def test_config_against_reference_program(exe, tmp_path, tag, follow):
     assert np.array_equal(a8[:, 1:4], ref[:, 1:4]), "true vehicle path"
     assert np.array_equal(a[-1, 1:4], g[tag + "_last"][1:4])
     n = ref.shape[0] if follow is None else follow // EVERY
-    scale = max(1.0, np.abs(ref[:, 1:3]).max())
-    d = np.abs(a8[:n, 4:6] - ref[:n, 4:6]).max()
+    scale = np.maximum(1.0, np.abs(ref[:n, 4:6]).max(axis=1))
+    d = (np.abs(a8[:n, 4:6] - ref[:n, 4:6]).max(axis=1) / scale).max()
     dt = np.abs((a8[:n, 6] - ref[:n, 6] + np.pi) % (2 * np.pi) - np.pi).max()
-    assert d <= 1e-4 * scale and dt <= 1e-4, (d, dt, scale)
+    assert d <= 1e-4 and dt <= 1e-4, (d, dt)
     # to the end of the run the estimate tracks the true path as well as the reference's own estimate does
     err_ref = np.abs(ref[:, 4:6] - ref[:, 1:3]).max()
     err = np.abs(a8[:, 4:6] - a8[:, 1:3]).max()
