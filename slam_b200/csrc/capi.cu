@@ -109,7 +109,8 @@ static void free_all(slamgpu *h) {
     if (h->log_stream) cudaStreamDestroy(h->log_stream);
     void *dev[] = {h->pose[0], h->pose[1], h->w, h->lm_mean, h->lm_cov, h->gauss, h->unif_base, h->di_base, h->cdf,
                    h->mloc, h->sel, h->keep, h->tot_slab, h->xflags, h->d_sc, h->d_z,
-                   h->d_rec_in, h->d_rec_out, h->d_est, h->keeplog, h->anc, h->d_phys, h->fb_list, h->fb_count};
+                   h->d_rec_in, h->d_rec_out, h->d_est, h->keeplog, h->anc, h->d_phys, h->fb_list, h->fb_count,
+                   h->gauss_flags};
     for (void *p : dev)
         if (p) cudaFree(p);
     if (h->h_sc) cudaFreeHost(h->h_sc);
@@ -194,6 +195,8 @@ static int create_impl(const slamgpu_config *cfg, slamgpu *h) {
         CU(cudaFuncSetAttribute(k_fs2_update_listed<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
         CU(cudaFuncSetAttribute(k_fs2_update_listed<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     }
+    CU(cudaMalloc(&h->gauss_flags, sizeof(unsigned) * SLAM_GAUSS_CHUNKS));
+    CU(cudaMemset(h->gauss_flags, 0, sizeof(unsigned) * SLAM_GAUSS_CHUNKS));
     h->obs_cap = 1024;
     CU(cudaMalloc(&h->d_z, (sizeof(float2) + 2 * sizeof(int)) * h->obs_cap));
     CU(cudaHostAlloc(&h->h_obs, (sizeof(float2) + 2 * sizeof(int)) * h->obs_cap * SLAM_OBS_SLOTS, cudaHostAllocDefault));
@@ -699,12 +702,18 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
     }
     const bool fs2 = h->cfg.method == SLAMGPU_FASTSLAM2;
     const float *dg = nullptr;
+    bool gauss_in_kernel = false;
     if (fs2 && (K > 0 || Kn > 0)) {
         if (gauss) {
             CU(cudaMemcpyAsync(h->gauss, gauss, sizeof(float) * 3 * h->P, cudaMemcpyHostToDevice, h->stream));
         } else if (h->gauss_inflight) {  // slamgpu_update put the copy on the copy stream: it overlaps the predict pass
-            CU(cudaStreamWaitEvent(h->stream, h->ev_gauss, 0));
-            h->gauss_inflight = false;
+            // ... and, chunk by chunk, the fast FastSLAM2 kernel itself, which waits for a chunk's flag where it
+            // first needs the noise; every other consumer waits for the whole buffer
+            gauss_in_kernel = h->gauss_chunked && K > 0 && h->cfg.math_mode == SLAMGPU_MATH_FAST;
+            if (!gauss_in_kernel) {
+                CU(cudaStreamWaitEvent(h->stream, h->ev_gauss, 0));
+                h->gauss_inflight = false;
+            }
         } else if (!(h->gauss_staged && h->gauss_rows_staged == 3)) {
             return slam_fail(SLAMGPU_EINVAL, "FastSLAM2 update needs gauss[3][P] (or slamgpu_stage_noise first)");
         }
@@ -752,18 +761,32 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
             const unsigned grid = grid_for(P, SLAM_UPDATE_THREADS), grid_l = std::min<unsigned>(grid, 148u * 4u);
             const size_t sm_f = SLAM_FS2_FAST_SMEM(K), sm_l = SLAM_OBS_FS2_SMEM(K);
             CU(cudaMemsetAsync(h->fb_count, 0, sizeof(int), h->stream));
+            GaussArrival ga = {nullptr, 0, nullptr};
+            if (gauss_in_kernel) {
+                ga.flags = h->gauss_flags;
+                ga.shift = h->gauss_shift();
+                ga.late = &h->d_sc->gauss_late;
+            }
             if (anc) {
                 k_fs2_update_fast<true><<<grid, SLAM_UPDATE_THREADS, sm_f, h->stream>>>(
-                    h->soa(h->cur), h->ring(), P, o, K, Rm, dg, anc, pr, Pgl, h->fb_list, h->fb_count);
+                    h->soa(h->cur), h->ring(), P, o, K, Rm, dg, ga, anc, pr, Pgl, h->fb_list, h->fb_count);
                 KCHECK();
                 LAUNCHED(h, SLAMGPU_T_UPDATE);
+                if (gauss_in_kernel) {  // the fallback-list kernel (and anything later) reads the whole buffer
+                    CU(cudaStreamWaitEvent(h->stream, h->ev_gauss, 0));
+                    h->gauss_inflight = false;
+                }
                 k_fs2_update_listed<true><<<grid_l, 128, sm_l, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, dg, anc,
                                                                             pr, Pgl, h->fb_list, h->fb_count);
             } else {
                 k_fs2_update_fast<false><<<grid, SLAM_UPDATE_THREADS, sm_f, h->stream>>>(
-                    h->soa(h->cur), h->ring(), P, o, K, Rm, dg, nullptr, pr, Pgl, h->fb_list, h->fb_count);
+                    h->soa(h->cur), h->ring(), P, o, K, Rm, dg, ga, nullptr, pr, Pgl, h->fb_list, h->fb_count);
                 KCHECK();
                 LAUNCHED(h, SLAMGPU_T_UPDATE);
+                if (gauss_in_kernel) {
+                    CU(cudaStreamWaitEvent(h->stream, h->ev_gauss, 0));
+                    h->gauss_inflight = false;
+                }
                 k_fs2_update_listed<false><<<grid_l, 128, sm_l, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, dg,
                                                                              nullptr, pr, Pgl, h->fb_list, h->fb_count);
             }
@@ -974,6 +997,11 @@ extern "C" int slamgpu_resample(slamgpu_t *h, const double *unif, int32_t *keep_
     RET(span_end(h, &sp));
     CU(cudaStreamSynchronize(h->stream));
     if (h->h_sc->pad[0]) return slam_fail(SLAMGPU_ECOMM, "a peer device never arrived at an exchange (sharded resample)");
+    h->gauss_chunked = false;
+    if (h->h_sc->gauss_late) {
+        cudaMemset(&h->d_sc->gauss_late, 0, sizeof(int));
+        return slam_fail(SLAMGPU_ECUDA, "the noise upload never arrived behind the update kernel");
+    }
     if (h->h_sc->anomaly) {
         // knife-edge ordering the search could not prove: run the exact sequential merge (core.cpp:800-806)
         if (h->world > 1) return slam_fail(SLAMGPU_ECOMM, "sequential keep[] fallback is not available when sharded");
@@ -1010,12 +1038,29 @@ extern "C" int slamgpu_update(slamgpu_t *h, const float *zf, const int32_t *idf,
             CU(cudaEventCreateWithFlags(&h->ev_gauss, cudaEventDisableTiming));
             CU(cudaEventCreateWithFlags(&h->ev_unif, cudaEventDisableTiming));
         }
+        const bool chunked = want_gauss && K > 0 && h->cfg.math_mode == SLAMGPU_MATH_FAST && h->P >= (1u << 16);
+        if (chunked) CU(cudaMemsetAsync(h->gauss_flags, 0, sizeof(unsigned) * SLAM_GAUSS_CHUNKS, h->stream));
         CU(cudaEventRecord(h->ev_in, h->stream));  // earlier readers of the two buffers are behind this point
         CU(cudaStreamWaitEvent(h->copy_stream, h->ev_in, 0));
+        if (chunked) RET(flush_predicts(h));  // the queued predict pass runs while the chunks are being enqueued
         if (want_gauss) {
-            CU(cudaMemcpyAsync(h->gauss, gauss, sizeof(float) * 3 * h->P, cudaMemcpyHostToDevice, h->copy_stream));
+            if (chunked) {
+                // column chunks in particle order, each followed by its arrival flag: the update kernel's CTAs run in
+                // the same order and wait per chunk (kernels.cuh gauss_arrived_load), so only the first chunk's
+                // transfer is exposed instead of all 12 B x P
+                const size_t C = (size_t) 1 << h->gauss_shift();
+                for (size_t c0 = 0, c = 0; c0 < h->P; c0 += C, c++) {
+                    const size_t n = std::min(C, h->P - c0);
+                    CU(cudaMemcpy2DAsync(h->gauss + c0, sizeof(float) * h->P, gauss + c0, sizeof(float) * h->P,
+                                         sizeof(float) * n, 3, cudaMemcpyHostToDevice, h->copy_stream));
+                    CU(cudaMemsetAsync(h->gauss_flags + c, 0xff, sizeof(unsigned), h->copy_stream));
+                }
+            } else {
+                CU(cudaMemcpyAsync(h->gauss, gauss, sizeof(float) * 3 * h->P, cudaMemcpyHostToDevice, h->copy_stream));
+            }
             CU(cudaEventRecord(h->ev_gauss, h->copy_stream));
             h->gauss_inflight = true;
+            h->gauss_chunked = chunked;
             h->gauss_staged = false;
         }
         if (unif) {

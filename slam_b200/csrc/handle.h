@@ -36,7 +36,9 @@ using slam::PoseSoA;
 struct Scalars {  // device + pinned mirror
     float ws, s2, csum, neff;
     int anomaly;
-    int pad[3];
+    int pad[3];      // [0] peer-exchange time-out; [1..2] 64-bit count of remote resample sources
+    int gauss_late;  // a chunk of an in-flight noise upload never arrived (GaussArrival); cleared by the host on error
+    int pad2[3];
 };
 
 struct TimedSpan {
@@ -99,6 +101,8 @@ struct slamgpu {
     cudaEvent_t ev_keep = nullptr, ev_log = nullptr;
     bool log_pending = false;
     bool gauss_inflight = false, unif_inflight = false;
+    bool gauss_chunked = false;       // the in-flight Gaussians carry per-chunk arrival flags (types.cuh GaussArrival)
+    unsigned *gauss_flags = nullptr;  // [SLAM_GAUSS_CHUNKS]
     int gauss_rows_staged = 0;
     // timing
     bool timing = false;
@@ -126,6 +130,11 @@ struct slamgpu {
     }
     int phys_row(int l) const { return phys[l]; }
     double *unif() const { return unif_base + 2; }
+    unsigned gauss_shift() const {  // log2 of the column chunk of a chunked noise upload: ceil(P / chunks), power of two
+        unsigned sh = 5;
+        while ((((size_t) 1 << sh) * SLAM_GAUSS_CHUNKS) < P) sh++;
+        return sh;
+    }
     float *di() const { return di_base + 2; }
 };
 

@@ -337,9 +337,40 @@ __device__ __forceinline__ void cp_async_wait() {
 // belong to the previous resample epoch is READ at column anc[p] of its old physical row and the updated landmark is
 // WRITTEN to column p of a fresh physical row, so the row needs no separate k_materialise_rows pass (one read + one
 // write of 24 B per particle-landmark saved on every update that follows a resample).
+// Waits until this warp's chunk of a noise buffer that is still being uploaded has landed (GaussArrival), then reads
+// the thread's three Gaussians with loads the compiler cannot move above the wait.
+__device__ __forceinline__ void gauss_arrived_load(const GaussArrival &ga, const float *gauss, size_t P, size_t p,
+                                                   float g3[3]) {
+    if (ga.flags) {
+        const unsigned am = __activemask();  // lanes that left for the fallback list are not here
+        if ((int) (threadIdx.x & 31) == __ffs(am) - 1) {
+            const unsigned *f = ga.flags + (p >> ga.shift);
+            unsigned v;
+            const long long t0 = clock64();
+            while (true) {
+                asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+                if (v) break;
+                if (clock64() - t0 > 4000000000ll) {  // ~2 s: the copy stream died
+                    *ga.late = 1;
+                    break;
+                }
+                __nanosleep(256);
+            }
+        }
+        __syncwarp(am);
+#pragma unroll
+        for (int c = 0; c < 3; c++)
+            asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(g3[c]) : "l"(gauss + c * P + p) : "memory");
+    } else {
+        g3[0] = gauss[p];
+        g3[1] = gauss[P + p];
+        g3[2] = gauss[2 * P + p];
+    }
+}
+
 template <bool REMAP>
 __global__ void __launch_bounds__(SLAM_UPDATE_THREADS, 7) k_fs2_update_fast(PoseSoA s, MapRing m, size_t P, ObsSet o, int K,
-                                                                         float4 Rm, const float *__restrict__ gauss,
+                                                                         float4 Rm, const float *gauss, GaussArrival ga,
                                                                          const int *__restrict__ anc, PeerRows pr,
                                                                          long long n_global,
                                                                          int *__restrict__ list, int *__restrict__ count) {
@@ -401,7 +432,8 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS, 7) k_fs2_update_fast(Pose
             }
         }
     }
-    const float g3[3] = {gauss[p], gauss[P + p], gauss[2 * P + p]};
+    float g3[3];
+    gauss_arrived_load(ga, gauss, P, p, g3);
     float xs[3];
     const float ratio = proposal_finish_fast(x0, L0, x, pi, g3, xs);
 

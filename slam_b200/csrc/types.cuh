@@ -56,6 +56,16 @@ struct PeerRows {  // landmark pools by rank, for kernels that read a particle's
     unsigned spread;  // 0, or the chunk stride of spread_block(): remote-heavy CTAs interleaved with local ones
 };
 
+// Host noise arriving behind a running kernel (slamgpu_update): the [3][P] Gaussians go up in SLAM_GAUSS_CHUNKS column
+// chunks on the copy stream, each followed by a write of its flag; a warp of the update kernel waits for the flag of
+// the chunk its particles sit in, right before it samples the pose.  flags == nullptr: the buffer is already whole.
+#define SLAM_GAUSS_CHUNKS 8
+struct GaussArrival {
+    const unsigned *flags;  // [SLAM_GAUSS_CHUNKS], nonzero once the chunk has landed
+    unsigned shift;         // chunk of particle p = p >> shift
+    int *late;              // raised when a flag never came (bounded wait)
+};
+
 struct RowPair {  // one row move of a materialisation: physical source row -> physical destination row
     int src, dst;
 };

@@ -358,3 +358,32 @@ def test_full_size_slices_1m_particles(sb, oracle):
     g2 = f.download()
     assert np.array_equal(g2["xv"], g["xv"][:, keep]) and np.array_equal(g2["lm_cov"], g["lm_cov"][:, keep])
     assert np.array_equal(g2["lm_mean"], g["lm_mean"][:, keep])
+
+
+def test_update_with_noise_arriving_behind_the_kernel(sb):
+    """slamgpu_update uploads host Gaussians in column chunks on a copy stream and the fast FastSLAM2 kernel waits, per
+    chunk, where it first needs them (GaussArrival, P >= 65536).  Two consecutive updates through that path must equal,
+    bit for bit, update_particles + resample on a second handle that receives the whole buffer first."""
+    from gpu_util import make_backend
+    P, Nf, K = (1 << 17) + 4096, 12, 6  # not a multiple of the chunk: the last chunk is short
+    d = synthetic_state(4096, Nf, K, seed=21)
+    rng = np.random.default_rng(22)
+    w = np.full(4096, np.float32(1.0 / P), np.float32)
+    zn = np.zeros((0, 2), np.float32)
+    A = make_backend(2, P, Nf, n_effective=int(0.75 * P), scan_mode=sb.SCAN_BLOCKED)
+    B = make_backend(2, P, Nf, n_effective=int(0.75 * P), scan_mode=sb.SCAN_BLOCKED)
+    for f in (A, B):
+        f.upload_tiled(d["xv"], d["Pv"], w, d["lm_mean"], d["lm_cov"], Nf)
+    for cycle in range(2):
+        gauss = rng.standard_normal((3, P)).astype(np.float32)
+        unif = rng.random(P)
+        for f in (A, B):
+            for t in range(8):  # 8 ticks with a changing steering angle: Pv is full rank again after the update zeroed it
+                f.predict(1.5, 0.05 * (t - 3), Q_DEFAULT, 0.025, 0.0)
+        neff_a, did_a = A.update(d["zf"], d["idf"], zn, d["R"], gauss, unif)
+        B.update_particles(d["zf"], d["idf"], zn, d["R"], gauss)
+        _, neff_b, did_b = B.resample(unif)
+        assert np.isfinite(neff_a) and neff_a == neff_b and did_a == did_b, (cycle, neff_a, neff_b, did_a, did_b)
+        a, b = A.download(), B.download()
+        for k in ("xv", "Pv", "w", "lm_mean", "lm_cov"):
+            assert np.array_equal(a[k], b[k], equal_nan=True), (cycle, k)
