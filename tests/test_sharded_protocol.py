@@ -3,7 +3,10 @@ one-piece oracle bit for bit.  Each rank holds half of the weights and runs, in 
 library runs per device (slam_b200/csrc/capi.cu: resample_indices): per-1024-block scans locally, block totals
 all-gathered in rank order, the same upper-level scan on every rank, CDF all-gathered, select[] from local uniforms
 with a 2-slot halo from the previous rank, first-exceedance search on running maxima, keep = max(G[c], G[c-1]).
-The device kernels themselves are checked on GPUs by tests/test_gpu_sharded.py."""
+The library moves the same data through peer memory (comm.cu k_xchg pushes the block totals and the halo, the search
+reads the peers' CDF in place); gloo all-gathers stand in for that here — what is checked is WHICH data every rank
+must see at each step and that the result is the one-piece oracle's.  The device kernels themselves are checked on
+GPUs by tests/test_gpu_sharded.py."""
 import os
 
 import numpy as np
