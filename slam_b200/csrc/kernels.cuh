@@ -811,40 +811,119 @@ __device__ __forceinline__ long long first_exceed(const SearchArgs &a, float s) 
     return (long long) (b0 + l);
 }
 
+// The monotone key the two-level search of first_exceed() walks, as one function of the global index: the running
+// maximum of the CDF = max(prefix maximum of the earlier blocks, in-block running maximum).
+__device__ __forceinline__ float running_max_at(const SearchArgs &a, long long i) {
+    const long long blk = i / SLAM_SCAN_BLOCK;
+    const float m = a.mloc[a.world > 1 ? (int) ((size_t) i / a.n_local) : 0][i];
+    return blk > 0 ? fmaxf(a.BM[blk - 1], m) : m;
+}
+
+// first_exceed() by a whole warp: 32 probes per round trip instead of one (two rounds over <= 1024 block maxima, two
+// over the 1024 running maxima of the block) — the dependent-load chain of the CTA leaders below is what bounds the
+// kernel.  Same answer: both walk the same monotone keys.  All lanes must call it; all return the result.
+template <typename Key>
+__device__ __forceinline__ int warp_first_true(int lo, int hi, Key key) {
+    // answer in [lo, hi]; key(i) is false below the answer and true from it on; hi itself is known (or defined) true
+    const int lane = threadIdx.x & 31;
+    while (lo < hi) {
+        const int span = hi - lo, step = (span + 31) >> 5;
+        const int idx = min(lo + (lane + 1) * step - 1, hi - 1);
+        const unsigned b = __ballot_sync(0xffffffffu, key(idx));
+        if (b == 0) {
+            lo = hi;
+        } else {
+            const int f = __ffs(b) - 1;
+            const int top = min(lo + (f + 1) * step - 1, hi - 1);
+            lo = (f == 0) ? lo : min(lo + f * step - 1, hi - 1) + 1;
+            hi = top;
+        }
+    }
+    return lo;
+}
+__device__ __forceinline__ long long warp_first_exceed(const SearchArgs &a, float s) {
+    const float *BM = a.BM;
+    const int blk = warp_first_true(0, a.nb_global, [&](int i) { return BM[i] > s; });
+    if (blk == a.nb_global) return (long long) a.n_global;
+    const size_t b0 = (size_t) blk * SLAM_SCAN_BLOCK;
+    const int len = (int) min((size_t) SLAM_SCAN_BLOCK, a.n_global - b0);
+    const float *mloc = a.mloc[a.world > 1 ? (int) (b0 / a.n_local) : 0] + b0;
+    return (long long) b0 + warp_first_true(0, len - 1, [&](int i) { return mloc[i] > s; });
+}
+
+// select[] is non-decreasing over a CTA's 256 slots, so every G of the CTA lies between the G of its first and of its
+// last slot: two threads find those with the full two-level search, the CTA stages the running maxima of that window
+// (a few hundred entries when the weights are not degenerate) in shared memory and every thread searches there —
+// ~20 dependent L2 round trips per slot become ~10 shared-memory steps.  A window beyond SLAM_SEARCH_WINDOW falls back
+// to the per-thread search.  Same G either way: the first index whose running maximum exceeds select[c].
+#define SLAM_SEARCH_WINDOW 2048
 __global__ void __launch_bounds__(256) k_search_keep(SearchArgs a) {
     __shared__ long long g_sh[256 + 2];
+    __shared__ long long win[2];
+    __shared__ float swin[2];
+    __shared__ float W[SLAM_SEARCH_WINDOW];
     const size_t c = (size_t) blockIdx.x * blockDim.x + threadIdx.x;  // local slot
     const size_t c0 = (size_t) blockIdx.x * blockDim.x;
+    const long long SENT = (long long) a.n_global;
     float s = 0.0f;
     long long g = -1;
     if (c < a.n_local) {
         s = select_value(a, c);
         a.sel[c] = s;
-        g = first_exceed(a, s);
+    }
+    const int n_here = (int) min((size_t) blockDim.x, a.n_local - c0);  // live slots of this CTA (>= 1)
+    {
+        // warps 0 and 1: G of the two slots before this CTA's first one (the halo; none before global slot 0).  Slots
+        // of the previous device are recomputed from its di/unif: across a device boundary the host passes di/unif
+        // with a 2-slot halo in front (see capi), so local index c0 - 2 + t is valid whenever the global slot exists.
+        // warps 2 and 3: G of the CTA's first and last slot = the window every other G lies in.
+        const int wid = threadIdx.x >> 5;
+        if (wid < 2) {
+            const long long gc = (long long) (a.slot_offset + c0) - 2 + wid;
+            long long gh = -1;
+            if (gc >= 0) {
+                const long long cl = (long long) c0 - 2 + wid;  // may be -1 / -2: halo stored before index 0
+                const double t = __dadd_rn((double) a.di[cl], __dmul_rn(a.unif[cl], (double) a.k));
+                gh = warp_first_exceed(a, __double2float_rn(__dsub_rn(t, (double) a.khalf)));
+            }
+            if ((threadIdx.x & 31) == 0) g_sh[wid] = gh;
+        } else if (wid < 4) {
+            const float sw = select_value(a, wid == 2 ? c0 : c0 + n_here - 1);
+            const long long gw = warp_first_exceed(a, sw);
+            if ((threadIdx.x & 31) == 0) {
+                swin[wid - 2] = sw;
+                win[wid - 2] = gw;
+            }
+        }
+    }
+    __syncthreads();
+    const long long w0 = win[0], w1 = min(win[1], SENT - 1);  // G of the last slot may be "none" (SENT)
+    const long long wlen = w1 - w0 + 1;
+    if (w0 < SENT && wlen <= SLAM_SEARCH_WINDOW) {
+        for (long long j = threadIdx.x; j < wlen; j += blockDim.x) W[j] = running_max_at(a, w0 + j);
+        __syncthreads();
+        if (c < a.n_local && (s < swin[0] || s > swin[1])) {
+            // select[] dipped by an ulp across a stratum boundary (u == 1.0 next to u == 0.0): outside the window's proof
+            g = first_exceed(a, s);
+        } else if (c < a.n_local) {
+            int lo = 0, hi = (int) wlen;  // first j with W[j] > s; hi == wlen: none inside the window
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (W[mid] > s) hi = mid; else lo = mid + 1;
+            }
+            // none inside the window can only mean "none at all": the window ends at the last slot's G or at the
+            // last particle
+            g = (lo < (int) wlen) ? w0 + lo : SENT;
+        }
+    } else if (c < a.n_local) {
+        g = (w0 >= SENT) ? SENT : first_exceed(a, s);
     }
     g_sh[threadIdx.x + 2] = g;
-    if (threadIdx.x < 2) {
-        // halo: G of the two slots before this CTA's first one (global slots; none before global slot 0).
-        // Slots of the previous device are recomputed from its di/unif only when they are local; across a device
-        // boundary the host passes di/unif with a 2-slot halo (see capi), so index c0 - 2 + t is valid when
-        // slot_offset + c0 >= 2 - t.
-        const long long gc = (long long) (a.slot_offset + c0) - 2 + threadIdx.x;
-        long long gh = -1;
-        if (gc >= 0) {
-            SearchArgs h = a;
-            const long long cl = (long long) c0 - 2 + threadIdx.x;  // may be -1 / -2: halo stored before index 0
-            const double t = __dadd_rn((double) a.di[cl], __dmul_rn(a.unif[cl], (double) a.k));
-            const float sh_ = __double2float_rn(__dsub_rn(t, (double) a.khalf));
-            gh = first_exceed(h, sh_);
-        }
-        g_sh[threadIdx.x] = gh;
-    }
     __syncthreads();
     if (c >= a.n_local) return;
     const long long g1 = g_sh[threadIdx.x + 1], g2 = g_sh[threadIdx.x];  // G[c-1], G[c-2]  (-1 if absent)
     const long long kc = max(g, g1);
     const long long kprev = max(g1, g2);  // K[c-1]; -1 when c is global slot 0
-    const long long SENT = (long long) a.n_global;
     bool ok;
     if (g >= kprev) ok = true;
     else ok = (kc == kprev) && (kprev == SENT || a.cdf[a.world > 1 ? (int) ((size_t) kprev / a.n_local) : 0][kprev] > s);

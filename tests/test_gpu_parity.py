@@ -78,6 +78,40 @@ def test_resample_blocked_bit_exact_vs_oracle(sb, oracle, N):
         assert np.array_equal(keep, keep_o), (N, trial, int((keep != keep_o).sum()))
 
 
+@pytest.mark.parametrize("pattern", ["gap", "one_heavy", "edges", "tail_zero"])
+def test_resample_search_window_cases(sb, oracle, pattern):
+    """k_search_keep stages the running maxima between the G of a CTA's first and last slot in shared memory and
+    searches there; these weight shapes drive it through its other paths: a window longer than the staging buffer
+    (zero-weight gaps), one particle owning every slot, uniforms of exactly 0 and 1 at stratum edges, and slots past
+    the end of the CDF (keep = -1)."""
+    from gpu_util import make_backend
+    N = 70000
+    rng = np.random.default_rng(5)
+    w = (rng.random(N).astype(np.float32) + np.float32(0.05))
+    unif = rng.integers(0, 2147483647, size=N) / float(2147483647)
+    if pattern == "gap":
+        w[1000:15000] = 0
+        w[30000:30500] = 0
+        w[40000:69990] = np.float32(1e-20)
+    elif pattern == "one_heavy":
+        w[:] = np.float32(1e-12)
+        w[33333] = 1
+    elif pattern == "edges":
+        unif[0::2] = 1.0
+        unif[1::2] = 0.0
+        unif[5000:5100] = 1.0
+        unif[9000:9100] = 0.0
+    elif pattern == "tail_zero":
+        w[N - 20000:] = 0
+        unif[N - 300:] = 1.0
+    f = make_backend(2, N, 4, n_effective=0, scan_mode=sb.SCAN_BLOCKED)
+    f.upload(w=w)
+    keep, neff, _ = f.resample(unif, want_keep=True)
+    wn, keep_o, neff_o = oracle.resample_indices(w, unif, scan_mode=1)
+    assert neff == neff_o and np.array_equal(f.download(landmarks=False)["w"], wn)
+    assert np.array_equal(keep, keep_o), (pattern, int((keep != keep_o).sum()))
+
+
 def test_resample_blocked_equals_sequential_on_exact_weights(sb, oracle):
     """Weights that are multiples of 2^-24 summing to <= 1 add exactly in any order: the blocked tree
     must then give the SAME keep[] as the reference's sequential order."""
