@@ -110,7 +110,7 @@ static void free_all(slamgpu *h) {
     void *dev[] = {h->pose[0], h->pose[1], h->w, h->lm_mean, h->lm_cov, h->gauss, h->unif_base, h->di_base, h->cdf,
                    h->mloc, h->sel, h->keep, h->tot_slab, h->xflags, h->d_sc, h->d_z,
                    h->d_rec_in, h->d_rec_out, h->d_est, h->keeplog, h->anc, h->d_phys, h->fb_list, h->fb_count,
-                   h->gauss_flags};
+                   h->gauss_flags, h->est_ticket};
     for (void *p : dev)
         if (p) cudaFree(p);
     if (h->h_sc) cudaFreeHost(h->h_sc);
@@ -187,6 +187,8 @@ static int create_impl(const slamgpu_config *cfg, slamgpu *h) {
     memset(h->h_sc, 0, sizeof(Scalars));
     h->est_blocks = 148 * 4;
     CU(cudaMalloc(&h->d_est, sizeof(EstPartial) * (h->est_blocks + 1)));
+    CU(cudaMalloc(&h->est_ticket, sizeof(unsigned)));
+    CU(cudaMemset(h->est_ticket, 0, sizeof(unsigned)));
     CU(cudaHostAlloc(&h->h_est, sizeof(EstPartial), cudaHostAllocDefault));
     {   // the FastSLAM2 fast kernels stage up to 2048 observations next to their landmark ring: > 48 KB
         const int big = (int) SLAM_FS2_FAST_SMEM(2048);
@@ -827,11 +829,13 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
 }
 
 // ---- resample ---------------------------------------------------------------------------------------------
-static int launch_upper(slamgpu *h, float *a0, float *s0, float *a1, float *s1, int n, int use_max) {
+static int launch_upper(slamgpu *h, float *a0, float *s0, float *a1, float *s1, int n, int use_max,
+                        float *recip1 = nullptr) {
     UpperArgs u;
     memset(&u, 0, sizeof(u));
     u.arr[0] = a0; u.sum_out[0] = s0;
     u.arr[1] = a1; u.sum_out[1] = s1;
+    u.recip_out[1] = recip1;
     u.n = n;
     u.use_max = use_max;
     k_scan_upper<<<a1 ? 2 : 1, SLAM_SCAN_BLOCK, 0, h->stream>>>(u);
@@ -879,10 +883,7 @@ static int resample_indices(slamgpu *h) {
         RET(comm_exchange(h->comm, h, arr, 2, false));
     }
     // D: recursive levels of both -> csum, s2
-    RET(launch_upper(h, h->tot_c, &d->csum, h->tot_s, &d->s2, (int) h->nbg, 0));
-    k_neff<<<1, 32, 0, h->stream>>>(&d->s2, &d->neff);
-    KCHECK();
-    LAUNCHED(h, SLAMGPU_T_WEIGHTS);
+    RET(launch_upper(h, h->tot_c, &d->csum, h->tot_s, &d->s2, (int) h->nbg, 0, &d->neff));  // nEff = 1 / sum(w^2)
     // E: final cdf + running maxima
     k_cdf_finalise<<<nb, SLAM_SCAN_BLOCK, 0, h->stream>>>(h->cdf + h->slot0, P, h->tot_c, b0, h->mloc + h->slot0,
                                                           h->bmax + b0);
@@ -937,8 +938,8 @@ static int resample_state(slamgpu *h) {
     h->epoch++;
     h->stat_resamples++;
     int *slot = h->keeplog + (size_t) (h->epoch % h->H) * Pg;
-    CU(cudaMemcpyAsync(slot + h->slot0, h->keep, sizeof(int) * P, cudaMemcpyDeviceToDevice, h->stream));
     if (h->world > 1) {
+        CU(cudaMemcpyAsync(slot + h->slot0, h->keep, sizeof(int) * P, cudaMemcpyDeviceToDevice, h->stream));
         // The peers' parts of this epoch's keep[] are only read by ancestor chains that START at a later epoch (a
         // chain's first step looks up its own slot, i.e. this device's part): the all-gather runs on its own stream
         // behind the coming predict / update and is waited for at the next resample.
@@ -960,7 +961,8 @@ static int resample_state(slamgpu *h) {
     if (h->world > 1) RET(comm_exchange(h->comm, h, nullptr, 0, false));
     k_gather_pose<<<grid_for(P, 256), 256, 0, h->stream>>>(pm, h->cur, h->pose[h->cur ^ 1], h->w, h->keep, P,
                                                            (long long) Pg, new_w, h->rank,
-                                                           (unsigned long long *) &h->d_sc->pad[1]);
+                                                           (unsigned long long *) &h->d_sc->pad[1],
+                                                           h->world > 1 ? nullptr : slot);
     KCHECK();
     LAUNCHED(h, SLAMGPU_T_GATHER);
     h->cur ^= 1;
@@ -1160,11 +1162,8 @@ extern "C" int slamgpu_estimate(slamgpu_t *h, double *x, double *y, double *t) {
     TimedSpan sp;
     RET(span_begin(h, SLAMGPU_T_ESTIMATE, &sp));
     PoseSoA s = h->soa(h->cur);
-    k_estimate_partial<<<h->est_blocks, 256, 0, h->stream>>>(s.xv, s.w, h->P, (long long) h->slot0, h->d_est);
-    KCHECK();
-    LAUNCHED(h, SLAMGPU_T_ESTIMATE);
-    k_estimate_final<<<1, 256, 0, h->stream>>>(h->d_est, h->est_blocks, s.xv, h->P, (long long) h->slot0,
-                                               h->d_est + h->est_blocks);
+    k_estimate<<<h->est_blocks, 256, 0, h->stream>>>(s.xv, s.w, h->P, (long long) h->slot0, h->d_est, h->est_ticket,
+                                                     h->d_est + h->est_blocks);
     KCHECK();
     LAUNCHED(h, SLAMGPU_T_ESTIMATE);
     CU(cudaMemcpyAsync(h->h_est, h->d_est + h->est_blocks, sizeof(EstPartial), cudaMemcpyDeviceToHost, h->stream));

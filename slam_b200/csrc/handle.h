@@ -103,6 +103,7 @@ struct slamgpu {
     bool gauss_inflight = false, unif_inflight = false;
     bool gauss_chunked = false;       // the in-flight Gaussians carry per-chunk arrival flags (types.cuh GaussArrival)
     unsigned *gauss_flags = nullptr;  // [SLAM_GAUSS_CHUNKS]
+    unsigned *est_ticket = nullptr;   // k_estimate's last-CTA counter (self-resetting)
     int gauss_rows_staged = 0;
     // timing
     bool timing = false;

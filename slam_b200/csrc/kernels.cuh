@@ -676,6 +676,7 @@ __global__ void __launch_bounds__(SLAM_SCAN_BLOCK) k_block_totals(const float *_
 struct UpperArgs {
     float *arr[3];
     float *sum_out[3];
+    float *recip_out[3];  // nullable: 1 / sum as one IEEE divide (nEff = 1 / sum(w^2), core.cpp:788-791)
     int n;
     int use_max;  // 1: max-scan (exact, order free) instead of the add scan
 };
@@ -708,8 +709,11 @@ __global__ void __launch_bounds__(SLAM_SCAN_BLOCK) k_scan_upper(UpperArgs a) {
         }
     }
     __syncthreads();
-    if (threadIdx.x == 0 && a.sum_out[blockIdx.x])
-        *a.sum_out[blockIdx.x] = (n > 1) ? __fadd_rn(x[n - 2], orig_last) : orig_last;
+    if (threadIdx.x == 0 && a.sum_out[blockIdx.x]) {
+        const float total = (n > 1) ? __fadd_rn(x[n - 2], orig_last) : orig_last;
+        *a.sum_out[blockIdx.x] = total;
+        if (a.recip_out[blockIdx.x]) *a.recip_out[blockIdx.x] = __fdiv_rn(1.0f, total);
+    }
 }
 
 // Step C: normalise (core.cpp:727-729 / 784-786: one quotient serves both), local CDF scan, totals of w and w^2.
@@ -999,9 +1003,6 @@ __global__ void k_reference_weights(float *__restrict__ w, size_t n, const float
     }
 }
 
-__global__ void k_neff(const float *__restrict__ s2, float *__restrict__ neff_out) {
-    if (threadIdx.x == 0 && blockIdx.x == 0) *neff_out = __fdiv_rn(1.0f, *s2);
-}
 
 // ---------------------------------------------------------------------------------------------------------
 // K7  resampling the state: particles[i] = old[keep[i]], w = 1/N (core.cpp:736-748).  keep < 0 (undefined behaviour in
@@ -1020,11 +1021,13 @@ __global__ void k_neff(const float *__restrict__ s2, float *__restrict__ neff_ou
 __global__ void __launch_bounds__(256) k_gather_pose(PeerMaps pm, int cur, float *__restrict__ dst_pose,
                                                      float *__restrict__ w, const int *__restrict__ keep, size_t P,
                                                      long long n_global, float new_w, int rank,
-                                                     unsigned long long *__restrict__ remote_sources) {
+                                                     unsigned long long *__restrict__ remote_sources,
+                                                     int *__restrict__ log_slot) {
     const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     int remote = 0;
     if (p < P) {
         long long k = keep[p];
+        if (log_slot) log_slot[p] = (int) k;  // this epoch's entry of the keep log (one device: no separate copy)
         if (k < 0) k = n_global - 1;
         const int r = (pm.world > 1) ? (int) (k / (long long) P) : 0;
         const size_t sidx = (size_t) (k - (long long) r * (long long) P);
@@ -1154,8 +1157,12 @@ __device__ __forceinline__ EstPartial est_block_reduce(EstPartial v) {
     }
     return v;
 }
-__global__ void __launch_bounds__(256) k_estimate_partial(const float *__restrict__ xv, const float *__restrict__ w,
-                                                          size_t P, long long offset, EstPartial *__restrict__ part) {
+// One launch: every CTA reduces its particles to a partial; the CTA that finishes last (ticket counter) combines the
+// partials in index order — the same order whichever CTA that is — and resets the ticket for the next call.
+__global__ void __launch_bounds__(256) k_estimate(const float *__restrict__ xv, const float *__restrict__ w, size_t P,
+                                                  long long offset, EstPartial *part, unsigned *ticket,
+                                                  EstPartial *__restrict__ out) {
+    __shared__ bool last;
     EstPartial v;
     v.sx = 0; v.sy = 0; v.wmax = -INFINITY; v.imax = 0x7fffffffffffffffLL;
     for (size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x; p < P; p += (size_t) gridDim.x * blockDim.x) {
@@ -1167,19 +1174,27 @@ __global__ void __launch_bounds__(256) k_estimate_partial(const float *__restric
         est_combine(v, o);
     }
     v = est_block_reduce(v);
-    if (threadIdx.x == 0) part[blockIdx.x] = v;
-}
-__global__ void __launch_bounds__(256) k_estimate_final(const EstPartial *__restrict__ part, int n,
-                                                        const float *__restrict__ xv, size_t P, long long offset,
-                                                        EstPartial *__restrict__ out) {
-    EstPartial v;
+    if (threadIdx.x == 0) {
+        part[blockIdx.x] = v;
+        __threadfence();
+        last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
     v.sx = 0; v.sy = 0; v.wmax = -INFINITY; v.imax = 0x7fffffffffffffffLL;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) est_combine(v, part[i]);
+    for (int i = threadIdx.x; i < (int) gridDim.x; i += blockDim.x) {
+        const volatile EstPartial *q = part + i;  // written by other CTAs of this launch: no cached / hoisted reads
+        EstPartial o;
+        o.sx = q->sx; o.sy = q->sy; o.wmax = q->wmax; o.theta = 0.0f; o.imax = q->imax;
+        est_combine(v, o);
+    }
     v = est_block_reduce(v);
     if (threadIdx.x == 0) {
         const long long loc = v.imax - offset;
         v.theta = (loc >= 0 && loc < (long long) P) ? xv[2 * P + (size_t) loc] : 0.0f;
         *out = v;
+        *ticket = 0;
     }
 }
 
