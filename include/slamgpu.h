@@ -181,9 +181,11 @@ int64_t slamgpu_launch_count(slamgpu_t *h);
 
 /* ---- sharding over several devices (one handle per device, one process per device) ------------------
  * Particles are block-partitioned: rank r holds global particles [r*P, (r+1)*P).  predict / update_particles
- * need no exchange.  Resampling exchanges (1) the per-1024-block weight totals (all-gather, rank order — the
- * blocked scan is then bit-identical to the one-device run), (2) the CDF, and (3) migrates resampled
- * particles.  The transport is NCCL; the caller distributes the 128-byte unique id. */
+ * need no exchange.  Resampling exchanges (1) the per-1024-block weight / CDF totals and block maxima in rank order
+ * (the blocked scan is then bit-identical to the one-device run), (2) searches the owning device's CDF in place and
+ * (3) migrates resampled particles — all three through peer memory (CUDA IPC over NVLink; the devices must be
+ * peer-accessible, i.e. one box).  NCCL carries the bootstrap and the log of keep[]; the caller distributes the
+ * 128-byte unique id.  SLAMGPU_STAT_REMOTE_SOURCES counts the particles that changed device. */
 int slamgpu_comm_unique_id(void *id128);
 int slamgpu_comm_init(slamgpu_t *h, int32_t rank, int32_t world, const void *id128);
 

@@ -1,11 +1,16 @@
 // comm.cu — exchange steps of the sharded resample, one process per device.
 //
-//   * small all-gathers (per-1024-block weight totals, block maxima, the CDF) and the 2-slot uniform halo go
-//     through NCCL, loaded at run time from libnccl.so.2 (the copy torch already mapped when the caller is a
-//     torchrun rank, else the system one) so that a single-device build has no NCCL dependency;
+//   * the small exchanges of the resample (per-1024-block weight totals, CDF totals, block maxima, the 2-slot uniform
+//     halo) and the stream-ordered barriers are ONE tiny kernel each over peer memory (k_xchg below): every rank
+//     stores its chunk into every peer's copy and waits on arrival counters; the CDF itself is never moved, the
+//     search reads it through the peer mappings;
 //   * particle migration is NOT a collective: every rank maps its peers' pose and landmark buffers (CUDA IPC over
-//     NVLink / NVSwitch) and the gather kernels (kernels.cuh K7) read particles[keep[i]] straight from the owning
-//     device, with a stream-ordered barrier between batches because freed physical rows are recycled.
+//     NVLink / NVSwitch) and the gather / update kernels (kernels.cuh K7, K3 REMAP) read particles[keep[i]] straight
+//     from the owning device, with a barrier between batches because freed physical rows are recycled;
+//   * NCCL remains for the bootstrap (the IPC handles travel in one all-gather), the all-gather of keep[] into the
+//     log (its own stream, off the critical path) and the SLAMGPU_XCHG_NCCL=1 A/B switch.  It is loaded at run time
+//     from libnccl.so.2 (the copy torch already mapped when the caller is a torchrun rank, else the system one) so
+//     that a single-device build has no NCCL dependency.
 #include <dlfcn.h>
 #include <nccl.h>
 

@@ -82,7 +82,7 @@ struct PredictArgs {
 struct EstPartial {
     double sx, sy;
     float wmax;
-    float theta;  // filled by k_estimate_final: heading of particle imax when it lives on this device
+    float theta;  // filled by k_estimate's last CTA: heading of particle imax when it lives on this device
     long long imax;
 };
 
