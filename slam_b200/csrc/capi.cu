@@ -280,6 +280,52 @@ extern "C" int64_t slamgpu_stat(slamgpu_t *h, int32_t which) {
     return 0;
 }
 
+// ---- cross-rank ordering without a barrier per kernel ------------------------------------------------------------------
+// Every rank issues the same kernels in the same order with the same row tables, and a rank's stream passes an
+// exchange (comm.cu k_xchg) only after every peer's stream has reached it.  So a kernel launched after exchange number
+// X knows that every peer has completed all kernels it launched before ITS exchange X.  A kernel that reads rows of a
+// peer (src) needs the peers' last writers of those rows complete; a kernel that overwrites rows (dst) needs the
+// peers' last remote readers of its copy complete.  Both hold as soon as ONE exchange lies between the two launches:
+// the tags below record the exchange count at the last write / remote read of every physical row and pose buffer, and
+// a barrier is issued only when a tag equals the current count (rare: the resample's own three exchanges usually lie
+// in between).  One device: nothing to do.
+static int xchg(slamgpu *h, const int *arrays, int narr, bool halo) {
+    RET(comm_exchange(h->comm, h, arrays, narr, halo));
+    h->xcount++;
+    return SLAMGPU_OK;
+}
+static int order_rows(slamgpu *h, const int *src, int ns, const int *dst, int nd) {
+    if (h->world <= 1) return SLAMGPU_OK;
+    if (h->row_written_x.size() != (size_t) h->rows_total) {
+        h->row_written_x.assign(h->rows_total, h->xcount);  // unknown history: as if touched just now
+        h->row_read_x.assign(h->rows_total, h->xcount);
+    }
+    bool need = false;
+    for (int i = 0; i < ns && !need; i++) need = h->row_written_x[src[i]] >= h->xcount;
+    for (int i = 0; i < nd && !need; i++)
+        need = h->row_read_x[dst[i]] >= h->xcount;
+    if (need) RET(xchg(h, nullptr, 0, false));
+    for (int i = 0; i < ns; i++) h->row_read_x[src[i]] = h->xcount;
+    for (int i = 0; i < nd; i++) h->row_written_x[dst[i]] = h->xcount;
+    return SLAMGPU_OK;
+}
+// After state was written from the host (uploads): every row and both pose buffers count as written just now.
+static void order_reset(slamgpu *h) {
+    h->row_written_x.clear();
+    h->row_read_x.clear();
+    for (int b = 0; b < 2; b++) h->pose_written_x[b] = h->pose_read_x[b] = h->xcount;
+}
+// Before a kernel that writes pose buffer `wbuf` (and, when rbuf >= 0, reads the peers' pose buffer rbuf).
+static int order_pose(slamgpu *h, int wbuf, int rbuf) {
+    if (h->world <= 1) return SLAMGPU_OK;
+    bool need = h->pose_read_x[wbuf] >= h->xcount;
+    if (rbuf >= 0) need = need || h->pose_written_x[rbuf] >= h->xcount;
+    if (need) RET(xchg(h, nullptr, 0, false));
+    h->pose_written_x[wbuf] = h->xcount;
+    if (rbuf >= 0) h->pose_read_x[rbuf] = h->xcount;
+    return SLAMGPU_OK;
+}
+
 // ---- deferred predict ticks ---------------------------------------------------------------------------------------
 static int flush_predicts(slamgpu *h) {
     if (h->predict_queue.empty()) return SLAMGPU_OK;
@@ -287,6 +333,7 @@ static int flush_predicts(slamgpu *h) {
     b.n = (int) h->predict_queue.size();
     for (int t = 0; t < b.n; t++) b.a[t] = h->predict_queue[t];
     h->predict_queue.clear();
+    RET(order_pose(h, h->cur, -1));
     TimedSpan sp;
     RET(span_begin(h, SLAMGPU_T_PREDICT, &sp));
     if (h->cfg.math_mode == SLAMGPU_MATH_FAST) {
@@ -406,8 +453,14 @@ static int materialise(slamgpu *h, const std::vector<int> &want) {
                 h->phys[l] = mv.p[q].dst;
                 h->row_epoch[l] = h->epoch;
             }
-            // sharded: a destination row was a source of an earlier chunk; no rank may overwrite it while a peer reads
-            if (h->world > 1) RET(comm_exchange(h->comm, h, nullptr, 0, false));
+            {   // sharded: sources are read on the peers, destinations may still be read by them (order_rows)
+                std::vector<int> srcs(n), dsts(n);
+                for (int q = 0; q < n; q++) {
+                    srcs[q] = mv.p[q].src;
+                    dsts[q] = mv.p[q].dst;
+                }
+                RET(order_rows(h, srcs.data(), n, dsts.data(), n));
+            }
             dim3 grid(grid_for(P, 256), (n + SLAM_GATHER_ROWS - 1) / SLAM_GATHER_ROWS);
             k_materialise_rows<<<grid, 256, 0, h->stream>>>(pm, h->ring(), P, anc_ptr, (long long) Pg, mv, n);
             KCHECK();
@@ -436,6 +489,7 @@ extern "C" int slamgpu_upload_particles(slamgpu_t *h, const float *xv, const flo
     if (Nf < 0) Nf = (lm_mean || lm_cov) ? h->Nf : -1;  // negative: keep the current landmark count
     CU(cudaSetDevice(h->cfg.device));
     RET(flush_predicts(h));
+    order_reset(h);
     const size_t P = h->P;
     PoseSoA s = h->soa(h->cur);
     if (xv) CU(cudaMemcpyAsync(s.xv, xv, sizeof(float) * 3 * P, cudaMemcpyHostToDevice, h->stream));
@@ -464,6 +518,7 @@ extern "C" int slamgpu_upload_particles_tiled(slamgpu_t *h, int64_t Pt, const fl
     if (Nf > 0 && (!lm_mean || !lm_cov)) return slam_fail(SLAMGPU_EINVAL, "landmark tile missing");
     CU(cudaSetDevice(h->cfg.device));
     RET(flush_predicts(h));
+    order_reset(h);
     const size_t P = h->P, T = (size_t) Pt;
     const int chunk = 64;  // landmark rows staged per copy
     float *dt = nullptr;
@@ -567,6 +622,7 @@ extern "C" int slamgpu_predict(slamgpu_t *h, float V, float G, const float Q[4],
         return SLAMGPU_OK;
     }
     RET(flush_predicts(h));
+    RET(order_pose(h, h->cur, -1));
     TimedSpan sp;
     RET(span_begin(h, SLAMGPU_T_PREDICT, &sp));
     k_predict<<<grid_for(h->P, 256), 256, 0, h->stream>>>(h->soa(h->cur), h->P, a, dg);
@@ -757,7 +813,14 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
             }
             pr.world = h->world;
             pr.spread = spread_stride(grid_for(P, fs2 ? SLAM_UPDATE_THREADS : 256), fs2 ? SLAM_UPDATE_THREADS : 256);
-            RET(comm_exchange(h->comm, h, nullptr, 0, false));
+        }
+        if (h->world > 1) {
+            // rows read at the ancestor's column on a peer (src != dst) / rows written (all): see order_rows
+            std::vector<int> srcs;
+            for (int i = 0; i < K; i++)
+                if (rows[i] != dst[i]) srcs.push_back(rows[i]);
+            RET(order_rows(h, srcs.data(), (int) srcs.size(), dst.data(), K));
+            RET(order_pose(h, h->cur, -1));
         }
         if (fs2 && fast) {
             const unsigned grid = grid_for(P, SLAM_UPDATE_THREADS), grid_l = std::min<unsigned>(grid, 148u * 4u);
@@ -813,6 +876,8 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
             rows[i] = h->phys_row(h->Nf + i);
             h->row_epoch[h->Nf + i] = h->epoch;
         }
+        RET(order_rows(h, nullptr, 0, rows.data(), Kn));
+        RET(order_pose(h, h->cur, -1));
         ObsSet o;
         RET(stage_obs_host(h, zn, rows.data(), nullptr, Kn, &o));
         const size_t smem = (sizeof(float2) + sizeof(int)) * Kn;
@@ -869,7 +934,7 @@ static int resample_indices(slamgpu *h) {
     LAUNCHED(h, SLAMGPU_T_WEIGHTS);
     if (h->world > 1) {
         const int arr[1] = {0};
-        RET(comm_exchange(h->comm, h, arr, 1, false));
+        RET(xchg(h, arr, 1, false));
     }
     // B: recursive levels -> ws
     RET(launch_upper(h, h->tot_w, &d->ws, nullptr, nullptr, (int) h->nbg, 0));
@@ -880,7 +945,7 @@ static int resample_indices(slamgpu *h) {
     LAUNCHED(h, SLAMGPU_T_WEIGHTS);
     if (h->world > 1) {
         const int arr[2] = {1, 2};
-        RET(comm_exchange(h->comm, h, arr, 2, false));
+        RET(xchg(h, arr, 2, false));
     }
     // D: recursive levels of both -> csum, s2
     RET(launch_upper(h, h->tot_c, &d->csum, h->tot_s, &d->s2, (int) h->nbg, 0, &d->neff));  // nEff = 1 / sum(w^2)
@@ -897,7 +962,7 @@ static int resample_indices(slamgpu *h) {
         // visible before any rank searches (and the next update's first exchange keeps a rank from overwriting its
         // CDF while a peer still searches it).
         const int arr[1] = {3};
-        RET(comm_exchange(h->comm, h, arr, 1, true));
+        RET(xchg(h, arr, 1, true));
     }
     RET(launch_upper(h, h->bmax, nullptr, nullptr, nullptr, (int) h->nbg, 1));
     // F: select + search
@@ -957,8 +1022,8 @@ static int resample_state(slamgpu *h) {
     PeerMaps pm;
     RET(peer_maps(h, &pm));
     // sharded: every rank's update kernels must be done before a peer reads its poses, and the buffer written here
-    // was the source of the previous resample
-    if (h->world > 1) RET(comm_exchange(h->comm, h, nullptr, 0, false));
+    // was the source of the previous resample: both are normally ordered by the three exchanges of resample_indices
+    RET(order_pose(h, h->cur ^ 1, h->cur));
     k_gather_pose<<<grid_for(P, 256), 256, 0, h->stream>>>(pm, h->cur, h->pose[h->cur ^ 1], h->w, h->keep, P,
                                                            (long long) Pg, new_w, h->rank,
                                                            (unsigned long long *) &h->d_sc->pad[1],

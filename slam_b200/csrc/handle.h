@@ -56,6 +56,12 @@ struct slamgpu {
     // landmark row pool (see kernels.cuh K7): logical -> physical table, free physical rows, and the resample epoch
     // each logical row's columns belong to
     std::vector<int> phys, free_rows;
+    // Sharded hazard tracking (capi.cu order_rows): the exchange count at which a physical row was last written /
+    // last read by a kernel that peers' copies of the same kernel may touch remotely.  One exchange between two
+    // kernels orders them across ranks (a rank passes an exchange only after every peer's stream has reached it).
+    long long xcount = 0;
+    std::vector<long long> row_written_x, row_read_x;
+    long long pose_written_x[2] = {-1, -1}, pose_read_x[2] = {-1, -1};
     std::vector<long long> row_epoch;
     long long epoch = 0;         // number of resamples applied to the poses so far
     int H = 0;                   // epochs of keep[] kept in the log
