@@ -133,7 +133,7 @@ static int setup_global(slamgpu *h) {
         }
     CU(cudaMalloc(&h->cdf, sizeof(float) * Pg));
     CU(cudaMalloc(&h->mloc, sizeof(float) * Pg));
-    CU(cudaMalloc(&h->tot_slab, sizeof(float) * 4 * h->nbg));
+    CU(cudaMalloc(&h->tot_slab, sizeof(float) * (4 * h->nbg + 2 * SLAM_MAX_RANKS * SLAM_XCHG_BLOB_WORDS)));
     h->tot_w = h->tot_slab;
     h->tot_c = h->tot_slab + h->nbg;
     h->tot_s = h->tot_slab + 2 * h->nbg;
@@ -189,7 +189,7 @@ static int create_impl(const slamgpu_config *cfg, slamgpu *h) {
     CU(cudaMalloc(&h->d_est, sizeof(EstPartial) * (h->est_blocks + 1)));
     CU(cudaMalloc(&h->est_ticket, sizeof(unsigned)));
     CU(cudaMemset(h->est_ticket, 0, sizeof(unsigned)));
-    CU(cudaHostAlloc(&h->h_est, sizeof(EstPartial), cudaHostAllocDefault));
+    CU(cudaHostAlloc(&h->h_est, sizeof(EstPartial) * SLAM_MAX_RANKS, cudaHostAllocDefault));
     {   // the FastSLAM2 fast kernels stage up to 2048 observations next to their landmark ring: > 48 KB
         const int big = (int) SLAM_FS2_FAST_SMEM(2048);
         CU(cudaFuncSetAttribute(k_fs2_update_fast<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
@@ -289,8 +289,9 @@ extern "C" int64_t slamgpu_stat(slamgpu_t *h, int32_t which) {
 // the tags below record the exchange count at the last write / remote read of every physical row and pose buffer, and
 // a barrier is issued only when a tag equals the current count (rare: the resample's own three exchanges usually lie
 // in between).  One device: nothing to do.
-static int xchg(slamgpu *h, const int *arrays, int narr, bool halo) {
-    RET(comm_exchange(h->comm, h, arrays, narr, halo));
+static int xchg(slamgpu *h, const int *arrays, int narr, bool halo, const void *blob = nullptr, int blob_bytes = 0,
+                int blob_slot = 0) {
+    RET(comm_exchange(h->comm, h, arrays, narr, halo, blob, blob_bytes, blob_slot));
     h->xcount++;
     return SLAMGPU_OK;
 }
@@ -1231,11 +1232,32 @@ extern "C" int slamgpu_estimate(slamgpu_t *h, double *x, double *y, double *t) {
                                                      h->d_est + h->est_blocks);
     KCHECK();
     LAUNCHED(h, SLAMGPU_T_ESTIMATE);
-    CU(cudaMemcpyAsync(h->h_est, h->d_est + h->est_blocks, sizeof(EstPartial), cudaMemcpyDeviceToHost, h->stream));
+    static_assert(sizeof(EstPartial) == 4 * SLAM_XCHG_BLOB_WORDS, "estimate record size");
+    if (h->world > 1) {
+        // every rank's partial lands in every rank's slab (peer stores, one exchange), then one read-back: no NCCL
+        // call, no second synchronisation.  Two landing areas by parity: a peer can be at most one exchange ahead.
+        const int slot = (int) (h->est_count++ & 1u);
+        RET(xchg(h, nullptr, 0, false, h->d_est + h->est_blocks, (int) sizeof(EstPartial), slot));
+        const float *area = h->tot_slab + 4 * h->nbg + (size_t) slot * SLAM_MAX_RANKS * SLAM_XCHG_BLOB_WORDS;
+        CU(cudaMemcpyAsync(h->h_est, area, sizeof(EstPartial) * h->world, cudaMemcpyDeviceToHost, h->stream));
+    } else {
+        CU(cudaMemcpyAsync(h->h_est, h->d_est + h->est_blocks, sizeof(EstPartial), cudaMemcpyDeviceToHost, h->stream));
+    }
     RET(span_end(h, &sp));
     CU(cudaStreamSynchronize(h->stream));
-    double sx = h->h_est->sx, sy = h->h_est->sy, th = h->h_est->theta;
-    if (h->world > 1) RET(comm_reduce_estimate(h->comm, h, &sx, &sy, h->h_est->wmax, h->h_est->imax, &th));
+    double sx = h->h_est[0].sx, sy = h->h_est[0].sy, th = h->h_est[0].theta;
+    float best = h->h_est[0].wmax;
+    long long bi = h->h_est[0].imax;
+    for (int r = 1; r < h->world; r++) {  // rank order: identical result on every rank
+        const EstPartial &e = h->h_est[r];
+        sx += e.sx;
+        sy += e.sy;
+        if (e.wmax > best || (e.wmax == best && e.imax < bi)) {
+            best = e.wmax;
+            bi = e.imax;
+            th = e.theta;
+        }
+    }
     if (x) *x = sx / (double) h->Pg;
     if (y) *y = sy / (double) h->Pg;
     if (t) *t = th;

@@ -213,6 +213,10 @@ __global__ void __launch_bounds__(256) k_xchg(const XchgArgs a) {
             for (int i = tid; i < a.count; i += blockDim.x) dst[i] = src[i];
         }
     }
+    if (a.blob_words && tid < a.blob_words * a.world) {
+        const int r = tid / a.blob_words, k = tid % a.blob_words;
+        reinterpret_cast<unsigned *>(a.slab[r])[a.blob_off + a.rank * a.blob_words + k] = a.blob_src[k];
+    }
     if (a.halo && a.rank + 1 < a.world && tid < 2)  // the next rank's search needs this rank's last two uniforms
         a.unif[a.rank + 1][tid] = a.unif[a.rank][a.P + tid];
     __threadfence_system();
@@ -234,10 +238,11 @@ __global__ void __launch_bounds__(256) k_xchg(const XchgArgs a) {
     __syncthreads();
 }
 
-int comm_exchange(SlamComm *c, slamgpu *h, const int *arrays, int narr, bool halo) {
+int comm_exchange(SlamComm *c, slamgpu *h, const int *arrays, int narr, bool halo, const void *blob, int blob_bytes,
+                  int blob_slot) {
     RET(open_peers(c, h));
     static const bool via_nccl = getenv("SLAMGPU_XCHG_NCCL") != nullptr;  // A/B switch: the same exchanges through NCCL
-    if (via_nccl) {
+    if (via_nccl && !blob) {  // (the estimate record always goes by peer memory)
         if (narr == 0 && !halo) return barrier(c, h->stream);
         NC(g_nccl.GroupStart());
         for (int k = 0; k < narr; k++) {
@@ -269,6 +274,11 @@ int comm_exchange(SlamComm *c, slamgpu *h, const int *arrays, int narr, bool hal
     a.halo = halo ? 1 : 0;
     a.P = h->P;
     a.error = &h->d_sc->pad[0];
+    if (blob) {
+        a.blob_src = (const unsigned *) blob;
+        a.blob_words = blob_bytes / 4;
+        a.blob_off = 4 * (int) h->nbg + blob_slot * SLAM_MAX_RANKS * SLAM_XCHG_BLOB_WORDS;
+    }
     k_xchg<<<1, 256, 0, h->stream>>>(a);
     if (cudaGetLastError() != cudaSuccess) return slam_fail(SLAMGPU_ECOMM, "peer-memory exchange launch failed");
     h->launches++;

@@ -110,6 +110,7 @@ struct slamgpu {
     bool gauss_chunked = false;       // the in-flight Gaussians carry per-chunk arrival flags (types.cuh GaussArrival)
     unsigned *gauss_flags = nullptr;  // [SLAM_GAUSS_CHUNKS]
     unsigned *est_ticket = nullptr;   // k_estimate's last-CTA counter (self-resetting)
+    unsigned est_count = 0;           // sharded: parity selects one of two landing areas for the peers' partials
     int gauss_rows_staged = 0;
     // timing
     bool timing = false;
@@ -161,7 +162,8 @@ int comm_barrier(SlamComm *c, cudaStream_t st);
 // Small exchange over peer memory instead of NCCL (latency: one 1-CTA kernel): all-gathers this rank's chunk
 // [b0, b0 + nb) of the listed block-total arrays (0 tot_w, 1 tot_c, 2 tot_s, 3 bmax), optionally sends the uniform
 // halo to the next rank, and is a stream-ordered barrier over all ranks.  narr == 0: barrier only.
-int comm_exchange(SlamComm *c, slamgpu *h, const int *arrays, int narr, bool halo);
+int comm_exchange(SlamComm *c, slamgpu *h, const int *arrays, int narr, bool halo, const void *blob = nullptr,
+                  int blob_bytes = 0, int blob_slot = 0);
 int comm_group_begin(SlamComm *c);
 int comm_group_end(SlamComm *c);
 int comm_allgather_i32(SlamComm *c, int *buf, size_t count, cudaStream_t st);

@@ -47,7 +47,12 @@ struct XchgArgs {
     int halo;
     unsigned long long P;
     int *error;            // set when a peer never arrived
+    // optional small record (the pose-estimate partial): blob_words 32-bit words from blob_src go to word offset
+    // blob_off + rank * blob_words of EVERY rank's slab (its own included), so that each rank ends up with all of them
+    const unsigned *blob_src;
+    int blob_words, blob_off;
 };
+#define SLAM_XCHG_BLOB_WORDS 8  // sizeof(EstPartial) / 4
 
 struct PeerRows {  // landmark pools by rank, for kernels that read a particle's ancestor column wherever it lives
     const float2 *mean[SLAM_MAX_RANKS];
