@@ -128,18 +128,7 @@ void comm_destroy(SlamComm *c) {
     delete c;
 }
 
-int comm_allgather_f32(SlamComm *c, float *buf, size_t count, cudaStream_t st) {
-    NC(g_nccl.AllGather(buf + (size_t) c->rank * count, buf, count, ncclFloat32, c->comm, st));
-    return SLAMGPU_OK;
-}
 
-int comm_halo_unif(SlamComm *c, double *unif_base, size_t P, cudaStream_t st) {
-    NC(g_nccl.GroupStart());
-    if (c->rank + 1 < c->world) NC(g_nccl.Send(unif_base + P, 2, ncclFloat64, c->rank + 1, c->comm, st));
-    if (c->rank > 0) NC(g_nccl.Recv(unif_base, 2, ncclFloat64, c->rank - 1, c->comm, st));
-    NC(g_nccl.GroupEnd());
-    return SLAMGPU_OK;
-}
 
 static int barrier(SlamComm *c, cudaStream_t st) {
     // stream-ordered: completes on a rank only once every rank's stream has reached it
@@ -192,7 +181,6 @@ int comm_peer_maps(SlamComm *c, slamgpu *h, PeerMaps *out) {
     return SLAMGPU_OK;
 }
 
-int comm_barrier(SlamComm *c, cudaStream_t st) { return barrier(c, st); }
 
 // ---- small exchanges over peer memory --------------------------------------------------------------------------------
 // The sharded resample needs three tiny all-gathers (<= 4 KB per rank) and a few barriers per update.  Through NCCL each
@@ -285,51 +273,8 @@ int comm_exchange(SlamComm *c, slamgpu *h, const int *arrays, int narr, bool hal
     return SLAMGPU_OK;
 }
 
-// Consecutive small exchanges issued between these two calls go out as ONE NCCL launch.
-int comm_group_begin(SlamComm *c) {
-    (void) c;
-    NC(g_nccl.GroupStart());
-    return SLAMGPU_OK;
-}
-int comm_group_end(SlamComm *c) {
-    (void) c;
-    NC(g_nccl.GroupEnd());
-    return SLAMGPU_OK;
-}
-
+// The one NCCL call on the data path: keep[] of every rank into every rank's log (capi.cu resample_state, own stream).
 int comm_allgather_i32(SlamComm *c, int *buf, size_t count, cudaStream_t st) {
     NC(g_nccl.AllGather(buf + (size_t) c->rank * count, buf, count, ncclInt32, c->comm, st));
-    return SLAMGPU_OK;
-}
-
-struct EstWire {
-    double sx, sy, theta;
-    long long imax;
-    float wmax;
-    float pad;
-};
-
-int comm_reduce_estimate(SlamComm *c, slamgpu *h, double *sx, double *sy, float wmax, long long imax, double *theta) {
-    EstWire mine;
-    mine.sx = *sx; mine.sy = *sy; mine.theta = *theta; mine.imax = imax; mine.wmax = wmax; mine.pad = 0;
-    EstWire *d = (EstWire *) c->d_small;
-    CU(cudaMemcpyAsync(d + c->rank, &mine, sizeof(mine), cudaMemcpyHostToDevice, h->stream));
-    NC(g_nccl.AllGather(d + c->rank, d, sizeof(EstWire), ncclChar, c->comm, h->stream));
-    CU(cudaMemcpyAsync(c->h_small, d, sizeof(EstWire) * c->world, cudaMemcpyDeviceToHost, h->stream));
-    CU(cudaStreamSynchronize(h->stream));
-    const EstWire *all = (const EstWire *) c->h_small;
-    double tx = 0, ty = 0, th = 0;
-    float best = -INFINITY;
-    long long bi = 0x7fffffffffffffffLL;
-    for (int r = 0; r < c->world; r++) {  // rank order: identical result on every rank
-        tx += all[r].sx;
-        ty += all[r].sy;
-        if (all[r].wmax > best || (all[r].wmax == best && all[r].imax < bi)) {
-            best = all[r].wmax;
-            bi = all[r].imax;
-            th = all[r].theta;
-        }
-    }
-    *sx = tx; *sy = ty; *theta = th;
     return SLAMGPU_OK;
 }

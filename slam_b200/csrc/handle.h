@@ -151,20 +151,13 @@ struct slamgpu {
 int comm_unique_id(void *id128, std::string *err);
 SlamComm *comm_create(int rank, int world, const void *id128, int device, std::string *err);
 void comm_destroy(SlamComm *c);
-// In-place all-gather over a global array: this rank's count elements sit at buf + rank*count.
-int comm_allgather_f32(SlamComm *c, float *buf, size_t count, cudaStream_t st);
-// unif_base[0..1] <- the previous rank's last two uniforms (the search kernel's 2-slot halo).
-int comm_halo_unif(SlamComm *c, double *unif_base, size_t P, cudaStream_t st);
 // Maps every peer's pose / landmark buffers (CUDA IPC, once) and returns the table the gather kernels index by rank.
 int comm_peer_maps(SlamComm *c, slamgpu *h, PeerMaps *out);
-// Stream-ordered barrier over all ranks (nobody passes until every rank's stream has reached it).
-int comm_barrier(SlamComm *c, cudaStream_t st);
 // Small exchange over peer memory instead of NCCL (latency: one 1-CTA kernel): all-gathers this rank's chunk
 // [b0, b0 + nb) of the listed block-total arrays (0 tot_w, 1 tot_c, 2 tot_s, 3 bmax), optionally sends the uniform
-// halo to the next rank, and is a stream-ordered barrier over all ranks.  narr == 0: barrier only.
+// halo to the next rank, optionally pushes a small record (blob) into one of two landing areas of every rank, and
+// is a stream-ordered barrier over all ranks.  narr == 0 and no blob: barrier only.
 int comm_exchange(SlamComm *c, slamgpu *h, const int *arrays, int narr, bool halo, const void *blob = nullptr,
                   int blob_bytes = 0, int blob_slot = 0);
-int comm_group_begin(SlamComm *c);
-int comm_group_end(SlamComm *c);
+// In-place NCCL all-gather over a global int array (the keep log): this rank's count elements sit at buf + rank*count.
 int comm_allgather_i32(SlamComm *c, int *buf, size_t count, cudaStream_t st);
-int comm_reduce_estimate(SlamComm *c, slamgpu *h, double *sx, double *sy, float wmax, long long imax, double *theta);
