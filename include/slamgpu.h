@@ -128,6 +128,21 @@ int slamgpu_predict(slamgpu_t *h, float V, float G, const float Q[4], float dt, 
 int slamgpu_update(slamgpu_t *h, const float *zf, const int32_t *idf, int32_t K, const float *zn, int32_t Kn,
                    const float R[4], const float *gauss, const double *unif, int32_t *did_resample, float *neff);
 
+/* slamgpu_update with the resample uniforms as the raw rand() values (4 bytes per particle instead of 8): the device
+ * forms unifRand() = rand() / double(RAND_MAX) itself, one IEEE division as core.cpp:776 — the same bits. */
+int slamgpu_update_i32(slamgpu_t *h, const float *zf, const int32_t *idf, int32_t K, const float *zn, int32_t Kn,
+                       const float R[4], const float *gauss, const int32_t *rand_ints, int32_t *did_resample,
+                       float *neff);
+
+/* Throughput mode.  The reference draws its noise INSIDE predict / update from rand() (fastslam2.cpp:353 ->
+ * core.cpp:452-458, 383-419; core.cpp:767, 775-777).  After slamgpu_seed, calls made with gauss == NULL / unif == NULL
+ * (and nothing staged) do the same on the device: a counter-based Philox4x32-10 keyed by `seed`, counter = (global
+ * particle index, draw number, stream), fed through the reference's own rand()/RAND_MAX and Box-Muller arithmetic
+ * (slam_b200/csrc/slam_rng.cuh; oracle/philox.py is its numpy twin).  The numbers do not depend on the sharding.
+ * predict_noise != 0 also draws the control noise of every predict tick (SWITCH_PREDICT_NOISE / FastSLAM1).
+ * Host-injected noise (parity mode) keeps working and takes precedence whenever it is passed or staged. */
+int slamgpu_seed(slamgpu_t *h, uint64_t seed, int32_t predict_noise);
+
 /* The two halves of slamgpu_update, for step-level parity checks. */
 int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int32_t *idf, int32_t K, const float *zn,
                              int32_t Kn, const float R[4], const float *gauss);
@@ -156,6 +171,22 @@ int slamgpu_estimate(slamgpu_t *h, double *x, double *y, double *t);
  * xv_out [3][n], lm_out [Nf][n][2] (nullable), n = ceil(P/stride). */
 int slamgpu_download_decimated(slamgpu_t *h, int64_t stride, float *xv_out, float *lm_out);
 
+/* A contiguous range [p0, p0 + n) of this handle's particles in the flat layout with P := n (any pointer may be
+ * NULL): what whole-state parity checks at 2^20 particles x 1024 landmarks use instead of a 25 GB download. */
+int slamgpu_download_slice(slamgpu_t *h, int64_t p0, int64_t n, float *xv, float *Pv, float *w, float *lm_mean,
+                           float *lm_cov);
+
+/* Parity instrumentation.  With capture on, every resample keeps a device copy of the weights as they entered it and
+ * as they left the normalisation; slamgpu_debug_read copies an item of the LAST resample to the host ([P] each):
+ * the weights before / after normalisation (float), keep[] (int32, global indices) and select[] (float).  The data
+ * path is otherwise unchanged (two device-to-device copies of 4 B per particle). */
+#define SLAMGPU_DEBUG_W_BEFORE 0
+#define SLAMGPU_DEBUG_W_NORMALISED 1
+#define SLAMGPU_DEBUG_KEEP 2
+#define SLAMGPU_DEBUG_SELECT 3
+int slamgpu_debug_capture(slamgpu_t *h, int32_t on);
+int slamgpu_debug_read(slamgpu_t *h, int32_t which, void *out);
+
 /* Device-time accounting per kernel family (CUDA events on the launching stream). */
 #define SLAMGPU_T_PREDICT 0
 #define SLAMGPU_T_UPDATE 1   /* the per-particle update kernel (FastSLAM1 or FastSLAM2) */
@@ -175,6 +206,7 @@ int slamgpu_timing_reset(slamgpu_t *h);
 #define SLAMGPU_STAT_CHAIN_STEPS 2
 #define SLAMGPU_STAT_REMOTE_SOURCES 4 /* sharded: resampled slots whose particle came from another device */
 #define SLAMGPU_STAT_ROWS_FUSED 3 /* of ROWS_MOVED: re-columned inside the FastSLAM2 update kernel itself (no extra pass) */
+#define SLAMGPU_STAT_KEEP_FALLBACKS 5 /* resamples whose keep[] came from the exact sequential merge (core.cpp:800-806) */
 int64_t slamgpu_stat(slamgpu_t *h, int32_t which);
 /* Total kernel launches issued by this handle since creation. */
 int64_t slamgpu_launch_count(slamgpu_t *h);

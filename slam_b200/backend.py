@@ -96,7 +96,30 @@ class FastSLAM:
         """rows re-columned by deferred resampling, resamples applied, ancestor-chain steps."""
         return dict(rows_moved=self._L.slamgpu_stat(self._h, 0), resamples=self._L.slamgpu_stat(self._h, 1),
                     chain_steps=self._L.slamgpu_stat(self._h, 2), rows_fused=self._L.slamgpu_stat(self._h, 3),
-                    remote_sources=self._L.slamgpu_stat(self._h, 4))
+                    remote_sources=self._L.slamgpu_stat(self._h, 4), keep_fallbacks=self._L.slamgpu_stat(self._h, 5))
+
+    def seed(self, seed, predict_noise=False):
+        """Throughput mode: noise the reference draws inside predict/update comes from the device generator."""
+        self._check(self._L.slamgpu_seed(self._h, int(seed), int(bool(predict_noise))))
+
+    def debug_capture(self, on=True):
+        self._check(self._L.slamgpu_debug_capture(self._h, int(on)))
+
+    def debug_read(self, which):
+        """0: weights entering the last resample, 1: after normalisation, 2: keep[], 3: select[]."""
+        out = np.empty(self.P, np.int32 if which == 2 else np.float32)
+        self._check(self._L.slamgpu_debug_read(self._h, int(which), out.ctypes.data))
+        return out
+
+    def download_slice(self, p0, n, landmarks=True):
+        Nf = self.Nf
+        out = dict(xv=np.empty((3, n), np.float32), Pv=np.empty((9, n), np.float32), w=np.empty(n, np.float32), Nf=Nf)
+        if landmarks and Nf:
+            out["lm_mean"] = np.empty((Nf, n, 2), np.float32)
+            out["lm_cov"] = np.empty((Nf, n, 4), np.float32)
+        self._check(self._L.slamgpu_download_slice(self._h, int(p0), int(n), _ptr(out["xv"]), _ptr(out["Pv"]),
+                                                   _ptr(out["w"]), _ptr(out.get("lm_mean")), _ptr(out.get("lm_cov"))))
+        return out
 
     def comm_init(self, rank, world, unique_id):
         buf = (C.c_char * 128).from_buffer_copy(bytes(unique_id))
@@ -192,11 +215,24 @@ class FastSLAM:
                                            C.byref(did), C.byref(neff)))
         return neff.value, bool(did.value)
 
-    def update_raw(self, zf_ptr, idf_ptr, K, R_ptr, gauss_ptr, unif_ptr):
-        """update() on raw host addresses (pinned buffers), no numpy marshalling: the benchmark's end-to-end call."""
+    def update_raw(self, zf_ptr, idf_ptr, K, R_ptr, gauss_ptr, unif_ptr, unif_ints=False):
+        """update() on raw host addresses (pinned buffers), no numpy marshalling: the benchmark's end-to-end call.
+        unif_ints: unif_ptr holds the raw rand() ints (slamgpu_update_i32) instead of doubles."""
         neff, did = C.c_float(), C.c_int32()
-        self._check(self._L.slamgpu_update(self._h, zf_ptr, idf_ptr, K, None, 0, R_ptr, gauss_ptr, unif_ptr,
-                                           C.byref(did), C.byref(neff)))
+        fn = self._L.slamgpu_update_i32 if unif_ints else self._L.slamgpu_update
+        self._check(fn(self._h, zf_ptr, idf_ptr, K, None, 0, R_ptr, gauss_ptr, unif_ptr, C.byref(did), C.byref(neff)))
+        return neff.value, bool(did.value)
+
+    def update_i32(self, zf, idf, zn, R, gauss, rand_ints):
+        """update() with the resample uniforms as the raw rand() values."""
+        zf, idf, zn = self._obs(zf, idf, zn)
+        R = _f32(R).ravel()
+        g = _f32(gauss)
+        r = np.ascontiguousarray(rand_ints, np.int32)
+        neff, did = C.c_float(), C.c_int32()
+        self._check(self._L.slamgpu_update_i32(self._h, _ptr(zf) if len(zf) else None, _ptr(idf) if len(idf) else None,
+                                               len(zf), _ptr(zn) if len(zn) else None, len(zn), _ptr(R), _ptr(g),
+                                               _ptr(r), C.byref(did), C.byref(neff)))
         return neff.value, bool(did.value)
 
     def compute_jacobians_batch(self, idf, R):

@@ -110,12 +110,13 @@ static void free_all(slamgpu *h) {
     void *dev[] = {h->pose[0], h->pose[1], h->w, h->lm_mean, h->lm_cov, h->gauss, h->unif_base, h->di_base, h->cdf,
                    h->mloc, h->sel, h->keep, h->tot_slab, h->xflags, h->d_sc, h->d_z,
                    h->d_rec_in, h->d_rec_out, h->d_est, h->keeplog, h->anc, h->d_phys, h->fb_list, h->fb_count,
-                   h->gauss_flags, h->est_ticket};
+                   h->gauss_flags, h->est_ticket, h->gbar, h->d_tail, h->d_chain, h->dbg_w, h->unif_i};
     for (void *p : dev)
         if (p) cudaFree(p);
     if (h->h_sc) cudaFreeHost(h->h_sc);
     if (h->h_obs) cudaFreeHost(h->h_obs);
-    if (h->h_est) cudaFreeHost(h->h_est);
+    if (h->h_tail) cudaFreeHost(h->h_tail);
+    if (h->h_ones) cudaFreeHost(h->h_ones);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     delete h;
 }
@@ -133,11 +134,24 @@ static int setup_global(slamgpu *h) {
         }
     CU(cudaMalloc(&h->cdf, sizeof(float) * Pg));
     CU(cudaMalloc(&h->mloc, sizeof(float) * Pg));
-    CU(cudaMalloc(&h->tot_slab, sizeof(float) * (4 * h->nbg + 2 * SLAM_MAX_RANKS * SLAM_XCHG_BLOB_WORDS)));
+    const size_t slab_words = SLAM_BLOB_BASE(h->nbg) + SLAM_XCHG_BLOB_SLOTS * SLAM_MAX_RANKS * SLAM_XCHG_BLOB_WORDS;
+    CU(cudaMalloc(&h->tot_slab, sizeof(float) * slab_words));
+    CU(cudaMemset(h->tot_slab, 0, sizeof(float) * slab_words));
     h->tot_w = h->tot_slab;
     h->tot_c = h->tot_slab + h->nbg;
     h->tot_s = h->tot_slab + 2 * h->nbg;
-    h->bmax = h->tot_slab + 3 * h->nbg;
+    h->lmax = h->tot_slab + 3 * h->nbg;
+    h->bm = h->tot_slab + 4 * h->nbg;
+    {   // the cooperative weights kernel: one CTA of 1024 threads per SM at most, all co-resident
+        h->coop_grid = 0;
+        int coop = 0, sms = 0, per_sm = 0;
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, h->cfg.device);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->cfg.device);
+        if (coop && !getenv("SLAMGPU_WEIGHTS_SPLIT") &&
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_weights_fused, SLAM_SCAN_BLOCK, 0) == cudaSuccess &&
+            per_sm >= 1)
+            h->coop_grid = (int) std::min<size_t>(h->nb, (size_t) sms);
+    }
     CU(cudaMalloc(&h->xflags, sizeof(unsigned long long) * SLAM_MAX_RANKS));
     CU(cudaMemset(h->xflags, 0, sizeof(unsigned long long) * SLAM_MAX_RANKS));
     if (h->keeplog) {
@@ -186,10 +200,20 @@ static int create_impl(const slamgpu_config *cfg, slamgpu *h) {
     CU(cudaHostAlloc(&h->h_sc, sizeof(Scalars), cudaHostAllocDefault));
     memset(h->h_sc, 0, sizeof(Scalars));
     h->est_blocks = 148 * 4;
-    CU(cudaMalloc(&h->d_est, sizeof(EstPartial) * (h->est_blocks + 1)));
+    CU(cudaMalloc(&h->d_est, sizeof(EstPartial) * h->est_blocks));
     CU(cudaMalloc(&h->est_ticket, sizeof(unsigned)));
     CU(cudaMemset(h->est_ticket, 0, sizeof(unsigned)));
-    CU(cudaHostAlloc(&h->h_est, sizeof(EstPartial) * SLAM_MAX_RANKS, cudaHostAllocDefault));
+    CU(cudaMalloc(&h->d_tail, sizeof(TailBlob)));
+    CU(cudaMemset(h->d_tail, 0, sizeof(TailBlob)));
+    CU(cudaMalloc(&h->d_chain, sizeof(TailBlob)));
+    CU(cudaMemset(h->d_chain, 0, sizeof(TailBlob)));
+    CU(cudaHostAlloc(&h->h_tail, sizeof(TailBlob) * SLAM_MAX_RANKS, cudaHostAllocDefault));
+    memset(h->h_tail, 0, sizeof(TailBlob) * SLAM_MAX_RANKS);
+    CU(cudaMalloc(&h->gbar, sizeof(unsigned)));
+    CU(cudaMemset(h->gbar, 0, sizeof(unsigned)));
+    CU(cudaHostAlloc(&h->h_ones, sizeof(unsigned), cudaHostAllocDefault));
+    *h->h_ones = 0xffffffffu;
+    h->force_anomaly = getenv("SLAMGPU_FORCE_ANOMALY") != nullptr;
     {   // the FastSLAM2 fast kernels stage up to 2048 observations next to their landmark ring: > 48 KB
         const int big = (int) SLAM_FS2_FAST_SMEM(2048);
         CU(cudaFuncSetAttribute(k_fs2_update_fast<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
@@ -255,12 +279,15 @@ extern "C" int slamgpu_set_stream(slamgpu_t *h, void *s) {
     return SLAMGPU_OK;
 }
 extern "C" void *slamgpu_get_stream(slamgpu_t *h) { return h ? (void *) h->stream : nullptr; }
+static int report_device_flags(slamgpu *h);
 extern "C" int slamgpu_synchronize(slamgpu_t *h) {
     if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
     CU(cudaSetDevice(h->cfg.device));
     RET(flush_predicts(h));
+    if (h->world > 1)  // an exchange that timed out anywhere since the last report must not go unnoticed
+        CU(cudaMemcpyAsync(h->h_sc, h->d_sc, sizeof(Scalars), cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
-    return SLAMGPU_OK;
+    return report_device_flags(h);
 }
 extern "C" int slamgpu_landmark_count(slamgpu_t *h) { return h ? h->Nf : SLAMGPU_EINVAL; }
 extern "C" int64_t slamgpu_launch_count(slamgpu_t *h) { return h ? h->launches : 0; }
@@ -271,11 +298,8 @@ extern "C" int64_t slamgpu_stat(slamgpu_t *h, int32_t which) {
         case SLAMGPU_STAT_RESAMPLES: return h->stat_resamples;
         case SLAMGPU_STAT_CHAIN_STEPS: return h->stat_chain_steps;
         case SLAMGPU_STAT_ROWS_FUSED: return h->stat_rows_fused;
-        case SLAMGPU_STAT_REMOTE_SOURCES: {  // as of the last weights read-back (lags the newest resample by one)
-            unsigned long long v;
-            memcpy(&v, &h->h_sc->pad[1], sizeof(v));
-            return (int64_t) v;
-        }
+        case SLAMGPU_STAT_REMOTE_SOURCES: return (int64_t) h->h_sc->remote_sources;  // as of the last read-back
+        case SLAMGPU_STAT_KEEP_FALLBACKS: return h->stat_keep_fallbacks;
     }
     return 0;
 }
@@ -327,9 +351,21 @@ static int order_pose(slamgpu *h, int wbuf, int rbuf) {
     return SLAMGPU_OK;
 }
 
+// Where a kernel's standard normals come from: the staged buffer, or (throughput mode) the device generator.
+static NoiseSrc noise_src(slamgpu *h, const float *staged, unsigned draw) {
+    NoiseSrc n;
+    n.gauss = staged;
+    n.seed = h->rng_seed;
+    n.slot0 = (unsigned long long) h->slot0;
+    n.draw = draw;
+    n.rng = staged ? 0 : 1;
+    return n;
+}
+
 // ---- deferred predict ticks ---------------------------------------------------------------------------------------
 static int flush_predicts(slamgpu *h) {
     if (h->predict_queue.empty()) return SLAMGPU_OK;
+    h->est_valid = false;
     PredictBatch b;
     b.n = (int) h->predict_queue.size();
     for (int t = 0; t < b.n; t++) b.a[t] = h->predict_queue[t];
@@ -491,6 +527,7 @@ extern "C" int slamgpu_upload_particles(slamgpu_t *h, const float *xv, const flo
     CU(cudaSetDevice(h->cfg.device));
     RET(flush_predicts(h));
     order_reset(h);
+    h->est_valid = false;
     const size_t P = h->P;
     PoseSoA s = h->soa(h->cur);
     if (xv) CU(cudaMemcpyAsync(s.xv, xv, sizeof(float) * 3 * P, cudaMemcpyHostToDevice, h->stream));
@@ -520,6 +557,7 @@ extern "C" int slamgpu_upload_particles_tiled(slamgpu_t *h, int64_t Pt, const fl
     CU(cudaSetDevice(h->cfg.device));
     RET(flush_predicts(h));
     order_reset(h);
+    h->est_valid = false;
     const size_t P = h->P, T = (size_t) Pt;
     const int chunk = 64;  // landmark rows staged per copy
     float *dt = nullptr;
@@ -617,7 +655,9 @@ extern "C" int slamgpu_predict(slamgpu_t *h, float V, float G, const float Q[4],
     a.sigma_phi = h->cfg.sigma_phi;
     a.method = h->cfg.method;
     a.use_heading = h->cfg.use_heading;
-    if (!dg) {  // no per-particle noise: queue the tick, apply the run of ticks in one pass over the poses
+    h->est_valid = false;
+    const bool rng_noise = !dg && h->rng_on && h->rng_predict_noise;  // throughput mode: control noise from the generator
+    if (!dg && !rng_noise) {  // no per-particle noise: queue the tick, apply the run of ticks in one pass over the poses
         h->predict_queue.push_back(a);
         if (h->predict_queue.size() >= SLAM_PREDICT_QUEUE) RET(flush_predicts(h));
         return SLAMGPU_OK;
@@ -626,7 +666,8 @@ extern "C" int slamgpu_predict(slamgpu_t *h, float V, float G, const float Q[4],
     RET(order_pose(h, h->cur, -1));
     TimedSpan sp;
     RET(span_begin(h, SLAMGPU_T_PREDICT, &sp));
-    k_predict<<<grid_for(h->P, 256), 256, 0, h->stream>>>(h->soa(h->cur), h->P, a, dg);
+    k_predict<<<grid_for(h->P, 256), 256, 0, h->stream>>>(h->soa(h->cur), h->P, a,
+                                                          noise_src(h, dg, rng_noise ? h->draw_control++ : 0));
     KCHECK();
     LAUNCHED(h, SLAMGPU_T_PREDICT);
     RET(span_end(h, &sp));
@@ -762,7 +803,9 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
     const bool fs2 = h->cfg.method == SLAMGPU_FASTSLAM2;
     const float *dg = nullptr;
     bool gauss_in_kernel = false;
+    h->est_valid = false;
     if (fs2 && (K > 0 || Kn > 0)) {
+        dg = h->gauss;
         if (gauss) {
             CU(cudaMemcpyAsync(h->gauss, gauss, sizeof(float) * 3 * h->P, cudaMemcpyHostToDevice, h->stream));
         } else if (h->gauss_inflight) {  // slamgpu_update put the copy on the copy stream: it overlaps the predict pass
@@ -774,10 +817,14 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
                 h->gauss_inflight = false;
             }
         } else if (!(h->gauss_staged && h->gauss_rows_staged == 3)) {
-            return slam_fail(SLAMGPU_EINVAL, "FastSLAM2 update needs gauss[3][P] (or slamgpu_stage_noise first)");
+            if (!h->rng_on)
+                return slam_fail(SLAMGPU_EINVAL,
+                                 "FastSLAM2 update needs gauss[3][P] (or slamgpu_stage_noise / slamgpu_seed first)");
+            dg = nullptr;  // throughput mode
         }
-        dg = h->gauss;
     }
+    // throughput mode (dg == nullptr): the pose sample's normals come from the device generator, one draw number per update
+    const NoiseSrc noise = noise_src(h, dg, (fs2 && !dg && (K > 0 || Kn > 0)) ? h->draw_pose++ : 0);
     const float4 Rm = make_float4(R[0], R[1], R[2], R[3]);
     const size_t P = h->P;
     if (K > 0) {
@@ -835,29 +882,29 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
             }
             if (anc) {
                 k_fs2_update_fast<true><<<grid, SLAM_UPDATE_THREADS, sm_f, h->stream>>>(
-                    h->soa(h->cur), h->ring(), P, o, K, Rm, dg, ga, anc, pr, Pgl, h->fb_list, h->fb_count);
+                    h->soa(h->cur), h->ring(), P, o, K, Rm, noise, ga, anc, pr, Pgl, h->fb_list, h->fb_count);
                 KCHECK();
                 LAUNCHED(h, SLAMGPU_T_UPDATE);
                 if (gauss_in_kernel) {  // the fallback-list kernel (and anything later) reads the whole buffer
                     CU(cudaStreamWaitEvent(h->stream, h->ev_gauss, 0));
                     h->gauss_inflight = false;
                 }
-                k_fs2_update_listed<true><<<grid_l, 128, sm_l, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, dg, anc,
-                                                                            pr, Pgl, h->fb_list, h->fb_count);
+                k_fs2_update_listed<true><<<grid_l, 128, sm_l, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, noise,
+                                                                            anc, pr, Pgl, h->fb_list, h->fb_count);
             } else {
                 k_fs2_update_fast<false><<<grid, SLAM_UPDATE_THREADS, sm_f, h->stream>>>(
-                    h->soa(h->cur), h->ring(), P, o, K, Rm, dg, ga, nullptr, pr, Pgl, h->fb_list, h->fb_count);
+                    h->soa(h->cur), h->ring(), P, o, K, Rm, noise, ga, nullptr, pr, Pgl, h->fb_list, h->fb_count);
                 KCHECK();
                 LAUNCHED(h, SLAMGPU_T_UPDATE);
                 if (gauss_in_kernel) {
                     CU(cudaStreamWaitEvent(h->stream, h->ev_gauss, 0));
                     h->gauss_inflight = false;
                 }
-                k_fs2_update_listed<false><<<grid_l, 128, sm_l, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, dg,
+                k_fs2_update_listed<false><<<grid_l, 128, sm_l, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, noise,
                                                                              nullptr, pr, Pgl, h->fb_list, h->fb_count);
             }
         } else if (fs2)
-            k_fs2_update<<<grid_for(P, 128), 128, smem, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, dg);
+            k_fs2_update<<<grid_for(P, 128), 128, smem, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, noise);
         else if (fast && anc)
             k_fs1_update_fast<true><<<grid_for(P, 256), 256, SLAM_OBS_FS2_SMEM(K), h->stream>>>(
                 h->soa(h->cur), h->ring(), P, o, K, Rm, anc, pr, Pgl);
@@ -885,7 +932,7 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
         TimedSpan sp;
         RET(span_begin(h, SLAMGPU_T_ADDFEAT, &sp));
         k_add_feature<<<grid_for(P, 256), 256, smem, h->stream>>>(h->soa(h->cur), h->ring(), P, o, Kn, Rm,
-                                                                   (fs2 && K == 0) ? 1 : 0, dg);
+                                                                   (fs2 && K == 0) ? 1 : 0, noise);
         KCHECK();
         LAUNCHED(h, SLAMGPU_T_ADDFEAT);
         RET(span_end(h, &sp));
@@ -895,31 +942,28 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
 }
 
 // ---- resample ---------------------------------------------------------------------------------------------
-static int launch_upper(slamgpu *h, float *a0, float *s0, float *a1, float *s1, int n, int use_max,
-                        float *recip1 = nullptr) {
-    UpperArgs u;
-    memset(&u, 0, sizeof(u));
-    u.arr[0] = a0; u.sum_out[0] = s0;
-    u.arr[1] = a1; u.sum_out[1] = s1;
-    u.recip_out[1] = recip1;
-    u.n = n;
-    u.use_max = use_max;
-    k_scan_upper<<<a1 ? 2 : 1, SLAM_SCAN_BLOCK, 0, h->stream>>>(u);
-    KCHECK();
-    LAUNCHED(h, SLAMGPU_T_WEIGHTS);
-    return SLAMGPU_OK;
-}
+// Where the resample uniforms of this call come from: the staged / uploaded double buffer, or the device generator.
+struct UnifChoice {
+    bool rng;
+    unsigned draw;
+};
 
-static int resample_indices(slamgpu *h) {
+static int resample_indices(slamgpu *h, const UnifChoice &uc) {
     const size_t P = h->P, Pg = h->Pg;
     const float k = (float) (1.0 / (float) Pg);
     const float khalf = k / 2;
     Scalars *d = h->d_sc;
-    CU(cudaMemsetAsync(&d->anomaly, 0, 2 * sizeof(int), h->stream));  // anomaly and pad[0] = exchange error
+    CU(cudaMemsetAsync(&h->d_tail->anomaly, 0, sizeof(int), h->stream));
     if (h->cfg.scan_mode == SLAMGPU_SCAN_REFERENCE) {
         if (h->world > 1) return slam_fail(SLAMGPU_EINVAL, "SLAMGPU_SCAN_REFERENCE is a one-device order");
-        k_reference_weights<<<1, 1, 0, h->stream>>>(h->w, P, h->di(), h->unif(), k, khalf, h->mloc, h->cdf, h->sel,
-                                                    &d->neff);
+        if (uc.rng) {  // the one-thread reference order reads its uniforms from the buffer
+            k_fill_unif<<<grid_for(P, 256), 256, 0, h->stream>>>(h->unif(), P, h->rng_seed, (unsigned long long) h->slot0,
+                                                                 uc.draw);
+            KCHECK();
+            LAUNCHED(h, SLAMGPU_T_WEIGHTS);
+        }
+        k_reference_weights<<<1, 1, 0, h->stream>>>(h->w, P, h->di(), h->unif(), k, khalf, h->mloc, h->cdf, h->sel, d,
+                                                    (float) h->cfg.n_effective, h->cfg.do_resample);
         KCHECK();
         LAUNCHED(h, SLAMGPU_T_WEIGHTS);
         k_keep_sequential<<<1, 1, 0, h->stream>>>(h->sel, h->cdf, h->keep, P);
@@ -927,58 +971,74 @@ static int resample_indices(slamgpu *h) {
         LAUNCHED(h, SLAMGPU_T_WEIGHTS);
         return SLAMGPU_OK;
     }
-    const unsigned nb = (unsigned) h->nb;
-    const size_t b0 = h->slot0 / SLAM_SCAN_BLOCK;  // first global block held here (P is a multiple of 1024 when sharded)
-    // A: block totals of w
-    k_block_totals<<<nb, SLAM_SCAN_BLOCK, 0, h->stream>>>(h->w, P, h->tot_w + b0);
-    KCHECK();
-    LAUNCHED(h, SLAMGPU_T_WEIGHTS);
-    if (h->world > 1) {
-        const int arr[1] = {0};
-        RET(xchg(h, arr, 1, false));
+    WeightsArgs wa;
+    wa.w = h->w;
+    wa.n = P;
+    wa.tot_w = h->tot_w;
+    wa.tot_c = h->tot_c;
+    wa.tot_s = h->tot_s;
+    wa.lmax = h->lmax;
+    wa.bm = h->bm;
+    wa.cdf_loc = h->cdf + h->slot0;
+    wa.mloc_loc = h->mloc + h->slot0;
+    wa.b0 = (int) (h->slot0 / SLAM_SCAN_BLOCK);  // first global block held here (P is a multiple of 1024 when sharded)
+    wa.nb = (int) h->nb;
+    wa.nbg = (int) h->nbg;
+    wa.sc = d;
+    wa.neff_threshold = (float) h->cfg.n_effective;
+    wa.do_resample = h->cfg.do_resample;
+    const int arr1[1] = {0}, arr2[3] = {1, 2, 3};
+    const bool halo = !uc.rng;  // the generator can produce any slot's uniform anywhere: nothing to send
+    if (h->coop_grid > 0) {
+        // ONE launch: both grid-wide barriers and (sharded) both exchanges happen inside the kernel
+        XchgArgs x1, x2;
+        memset(&x1, 0, sizeof(x1));
+        memset(&x2, 0, sizeof(x2));
+        x1.world = x2.world = 1;
+        if (h->world > 1) {
+            RET(comm_fill_xchg(h->comm, h, arr1, 1, halo, nullptr, 0, 0, &x1));
+            RET(comm_fill_xchg(h->comm, h, arr2, 3, false, nullptr, 0, 0, &x2));
+            h->xcount += 2;
+        }
+        GridBar gb = {h->gbar, h->gbar_base};
+        void *args[] = {(void *) &wa, (void *) &gb, (void *) &x1, (void *) &x2};
+        CU(cudaLaunchCooperativeKernel((const void *) k_weights_fused, dim3(h->coop_grid), dim3(SLAM_SCAN_BLOCK), args, 0,
+                                       h->stream));
+        h->gbar_base += SLAM_GRIDBAR_TICKS((unsigned) h->coop_grid);
+        LAUNCHED(h, SLAMGPU_T_WEIGHTS);
+    } else {
+        k_weights_a<<<wa.nb, SLAM_SCAN_BLOCK, 0, h->stream>>>(wa);
+        KCHECK();
+        LAUNCHED(h, SLAMGPU_T_WEIGHTS);
+        if (h->world > 1) RET(xchg(h, arr1, 1, halo));
+        k_weights_c<<<wa.nb, SLAM_SCAN_BLOCK, 0, h->stream>>>(wa);
+        KCHECK();
+        LAUNCHED(h, SLAMGPU_T_WEIGHTS);
+        if (h->world > 1) RET(xchg(h, arr2, 3, false));
+        k_weights_d<<<2, SLAM_SCAN_BLOCK, 0, h->stream>>>(wa);
+        KCHECK();
+        LAUNCHED(h, SLAMGPU_T_WEIGHTS);
     }
-    // B: recursive levels -> ws
-    RET(launch_upper(h, h->tot_w, &d->ws, nullptr, nullptr, (int) h->nbg, 0));
-    // C: normalise, local cdf scan, totals
-    k_normalise_scan<<<nb, SLAM_SCAN_BLOCK, 0, h->stream>>>(h->w, P, &d->ws, h->cdf + h->slot0, h->tot_c + b0,
-                                                            h->tot_s + b0);
-    KCHECK();
-    LAUNCHED(h, SLAMGPU_T_WEIGHTS);
-    if (h->world > 1) {
-        const int arr[2] = {1, 2};
-        RET(xchg(h, arr, 2, false));
-    }
-    // D: recursive levels of both -> csum, s2
-    RET(launch_upper(h, h->tot_c, &d->csum, h->tot_s, &d->s2, (int) h->nbg, 0, &d->neff));  // nEff = 1 / sum(w^2)
-    // E: final cdf + running maxima
-    k_cdf_finalise<<<nb, SLAM_SCAN_BLOCK, 0, h->stream>>>(h->cdf + h->slot0, P, h->tot_c, b0, h->mloc + h->slot0,
-                                                          h->bmax + b0);
-    KCHECK();
-    LAUNCHED(h, SLAMGPU_T_WEIGHTS);
+    // select + search.  The peers' in-block CDFs are read in place through the peer mappings; they were complete
+    // before the second exchange, and a rank overwrites them only after the next update's first exchange.
     PeerMaps pm;
     RET(peer_maps(h, &pm));
-    if (h->world > 1) {
-        // the block maxima are exchanged; the CDF and its running maxima stay where they are and are read through the
-        // peer mappings.  This exchange is also the stream-ordered barrier that makes every rank's k_cdf_finalise
-        // visible before any rank searches (and the next update's first exchange keeps a rank from overwriting its
-        // CDF while a peer still searches it).
-        const int arr[1] = {3};
-        RET(xchg(h, arr, 1, true));
-    }
-    RET(launch_upper(h, h->bmax, nullptr, nullptr, nullptr, (int) h->nbg, 1));
-    // F: select + search
     SearchArgs a;
     a.di = h->di();
-    a.unif = h->unif();
+    a.unif = uc.rng ? nullptr : h->unif();
+    a.seed = h->rng_seed;
+    a.draw = uc.draw;
     for (int r = 0; r < SLAM_MAX_RANKS; r++) {
         a.cdf[r] = pm.cdf[r];
         a.mloc[r] = pm.mloc[r];
     }
     a.world = h->world;
-    a.BM = h->bmax;
+    a.Tc = h->tot_c;
+    a.BM = h->bm;
     a.sel = h->sel;
     a.keep = h->keep;
-    a.anomaly = &d->anomaly;
+    a.anomaly = &h->d_tail->anomaly;
+    a.force_anomaly = h->force_anomaly ? 1 : 0;
     a.n_local = P;
     a.n_global = Pg;
     a.slot_offset = h->slot0;
@@ -991,18 +1051,148 @@ static int resample_indices(slamgpu *h) {
     return SLAMGPU_OK;
 }
 
-// The "particles[i] = oldParticles[keep[i]]" of core.cpp:739-748: poses now, maps deferred (kernels.cuh K7).
-static int resample_state(slamgpu *h) {
+// The pose half of "particles[i] = oldParticles[keep[i]]" (core.cpp:739-748) into the second pose buffer.  cond: the
+// device-side decision (nullptr = unconditional).  The buffers are flipped by resample_commit once the host knows.
+static int launch_gather_pose(slamgpu *h, const int *cond) {
     const size_t P = h->P, Pg = h->Pg;
     const float new_w = 1.0f / (float) Pg;
+    PeerMaps pm;
+    RET(peer_maps(h, &pm));
+    // sharded: every rank's update kernels must be done before a peer reads its poses, and the buffer written here
+    // was the source of the previous resample: both are normally ordered by the exchanges of resample_indices
+    RET(order_pose(h, h->cur ^ 1, h->cur));
+    // one device: the kernel also writes this epoch's entry of the keep log.  Slot (epoch + 1) % H holds an epoch no
+    // row can still need (materialise keeps every row within H - 1 epochs), so writing it before the decision is known
+    // is harmless when the decision turns out to be "no resample".
+    int *slot = h->keeplog + (size_t) ((h->epoch + 1) % h->H) * Pg;
     TimedSpan sg;
     RET(span_begin(h, SLAMGPU_T_GATHER, &sg));
+    k_gather_pose<<<grid_for(P, 256), 256, 0, h->stream>>>(pm, h->cur, h->pose[h->cur ^ 1], h->w, h->keep, P,
+                                                           (long long) Pg, new_w, h->rank, &h->d_sc->remote_sources,
+                                                           h->world > 1 ? nullptr : slot, cond);
+    KCHECK();
+    LAUNCHED(h, SLAMGPU_T_GATHER);
+    RET(span_end(h, &sg));
+    return SLAMGPU_OK;
+}
+
+// K8 into the tail record.  pick: device flag selecting the freshly gathered pose buffer (nullptr: the current one).
+static int launch_estimate(slamgpu *h, const int *pick) {
+    TimedSpan sp;
+    RET(span_begin(h, SLAMGPU_T_ESTIMATE, &sp));
+    k_estimate<<<h->est_blocks, 256, 0, h->stream>>>(h->pose[h->cur], h->pose[h->cur ^ 1], pick, h->w, h->P,
+                                                     (long long) h->slot0, h->d_est, h->est_ticket, &h->d_tail->est);
+    KCHECK();
+    LAUNCHED(h, SLAMGPU_T_ESTIMATE);
+    RET(span_end(h, &sp));
+    return SLAMGPU_OK;
+}
+
+// The tail record of every rank into pinned memory (sharded: one exchange pushes it into every rank's slab first —
+// that exchange is also how the ranks agree on the anomaly flag).
+static int fetch_tail(slamgpu *h) {
+    static_assert(sizeof(TailBlob) == 4 * SLAM_XCHG_BLOB_WORDS, "tail record size");
+    if (h->world > 1) {
+        // two landing areas by parity: a peer can be at most one exchange ahead
+        const int slot = (int) (h->tail_count++ & 1u);
+        RET(xchg(h, nullptr, 0, false, h->d_tail, (int) sizeof(TailBlob), slot));
+        const float *area = h->tot_slab + SLAM_BLOB_BASE(h->nbg) + (size_t) slot * SLAM_MAX_RANKS * SLAM_XCHG_BLOB_WORDS;
+        CU(cudaMemcpyAsync(h->h_tail, area, sizeof(TailBlob) * h->world, cudaMemcpyDeviceToHost, h->stream));
+    } else {
+        CU(cudaMemcpyAsync(h->h_tail, h->d_tail, sizeof(TailBlob), cudaMemcpyDeviceToHost, h->stream));
+    }
+    CU(cudaMemcpyAsync(h->h_sc, h->d_sc, sizeof(Scalars), cudaMemcpyDeviceToHost, h->stream));
+    return SLAMGPU_OK;
+}
+
+// Errors the device raised since the last report (sticky flags in Scalars): checked at every host synchronisation
+// that follows an exchange or an in-kernel wait, cleared only here.
+static int report_device_flags(slamgpu *h) {
+    if (h->h_sc->comm_error) {
+        cudaMemsetAsync(&h->d_sc->comm_error, 0, sizeof(int), h->stream);
+        h->h_sc->comm_error = 0;
+        return slam_fail(SLAMGPU_ECOMM, "a peer device never arrived at an exchange (sharded resample)");
+    }
+    if (h->h_sc->gauss_late) {
+        cudaMemsetAsync(&h->d_sc->gauss_late, 0, sizeof(int), h->stream);
+        h->h_sc->gauss_late = 0;
+        return slam_fail(SLAMGPU_ECUDA, "the noise upload never arrived behind the update kernel");
+    }
+    return SLAMGPU_OK;
+}
+
+// Rank-order combine of the tail records: identical result on every rank.
+static void combine_estimate(slamgpu *h) {
+    double sx = h->h_tail[0].est.sx, sy = h->h_tail[0].est.sy, th = h->h_tail[0].est.theta;
+    float best = h->h_tail[0].est.wmax;
+    long long bi = h->h_tail[0].est.imax;
+    for (int r = 1; r < h->world; r++) {
+        const EstPartial &e = h->h_tail[r].est;
+        sx += e.sx;
+        sy += e.sy;
+        if (e.wmax > best || (e.wmax == best && e.imax < bi)) {
+            best = e.wmax;
+            bi = e.imax;
+            th = e.theta;
+        }
+    }
+    h->est_x = sx / (double) h->Pg;
+    h->est_y = sy / (double) h->Pg;
+    h->est_t = th;
+    h->est_valid = true;
+}
+
+// keep[] by the exact sequential merge (core.cpp:800-806) when some rank's search met a slot it could not prove.
+// One device: one thread over the final CDF.  Sharded: the merge is inherently sequential, so the ranks take turns
+// in rank order — rank r continues from the CDF position rank r-1 ended at, which travels in the third landing area.
+static int keep_fallback(slamgpu *h) {
+    const size_t P = h->P, Pg = h->Pg;
+    PeerMaps pm;
+    RET(peer_maps(h, &pm));
+    // the final CDF of this device's slots into its mloc block (the search is done with the running maxima)
+    k_cdf_final<<<grid_for(P, 256), 256, 0, h->stream>>>(h->cdf + h->slot0, h->tot_c, (long long) h->slot0, P,
+                                                         h->mloc + h->slot0);
+    KCHECK();
+    LAUNCHED(h, SLAMGPU_T_WEIGHTS);
+    if (h->world <= 1) {
+        k_keep_sequential<<<1, 1, 0, h->stream>>>(h->sel, h->mloc, h->keep, P);
+        KCHECK();
+        LAUNCHED(h, SLAMGPU_T_WEIGHTS);
+        return SLAMGPU_OK;
+    }
+    RET(xchg(h, nullptr, 0, false));  // every rank's final CDF is in place
+    SeqArgs q;
+    for (int r = 0; r < SLAM_MAX_RANKS; r++) q.cdf[r] = pm.mloc[r];
+    q.sel = h->sel;
+    q.keep = h->keep;
+    q.n_local = P;
+    q.n_global = Pg;
+    const long long *area = (const long long *) (h->tot_slab + SLAM_BLOB_BASE(h->nbg) +
+                                                 (size_t) 2 * SLAM_MAX_RANKS * SLAM_XCHG_BLOB_WORDS);
+    for (int r = 0; r < h->world; r++) {
+        if (r == h->rank) {
+            q.start = r > 0 ? area + (size_t) (r - 1) * (SLAM_XCHG_BLOB_WORDS / 2) : nullptr;
+            q.end = (long long *) h->d_chain;
+            k_keep_sequential_part<<<1, 1, 0, h->stream>>>(q);
+            KCHECK();
+            LAUNCHED(h, SLAMGPU_T_WEIGHTS);
+        }
+        RET(xchg(h, nullptr, 0, false, h->d_chain, (int) sizeof(TailBlob), 2));
+    }
+    return SLAMGPU_OK;
+}
+
+// What follows a resample that did happen, once the host knows: the pose buffers flip, keep[] joins the log, and the
+// background trickle re-columns the stalest landmark rows (the maps themselves are not copied, kernels.cuh K7).
+static int resample_commit(slamgpu *h) {
+    const size_t P = h->P, Pg = h->Pg;
     if (h->log_pending) {  // the previous epoch's log must be whole before ancestor chains step through it
         CU(cudaStreamWaitEvent(h->stream, h->ev_log, 0));
         h->log_pending = false;
     }
     h->epoch++;
     h->stat_resamples++;
+    h->cur ^= 1;
     int *slot = h->keeplog + (size_t) (h->epoch % h->H) * Pg;
     if (h->world > 1) {
         CU(cudaMemcpyAsync(slot + h->slot0, h->keep, sizeof(int) * P, cudaMemcpyDeviceToDevice, h->stream));
@@ -1020,19 +1210,6 @@ static int resample_state(slamgpu *h) {
         CU(cudaEventRecord(h->ev_log, h->log_stream));
         h->log_pending = true;
     }
-    PeerMaps pm;
-    RET(peer_maps(h, &pm));
-    // sharded: every rank's update kernels must be done before a peer reads its poses, and the buffer written here
-    // was the source of the previous resample: both are normally ordered by the three exchanges of resample_indices
-    RET(order_pose(h, h->cur ^ 1, h->cur));
-    k_gather_pose<<<grid_for(P, 256), 256, 0, h->stream>>>(pm, h->cur, h->pose[h->cur ^ 1], h->w, h->keep, P,
-                                                           (long long) Pg, new_w, h->rank,
-                                                           (unsigned long long *) &h->d_sc->pad[1],
-                                                           h->world > 1 ? nullptr : slot);
-    KCHECK();
-    LAUNCHED(h, SLAMGPU_T_GATHER);
-    h->cur ^= 1;
-    RET(span_end(h, &sg));
     // background trickle: the stalest rows, enough per resample that no row's backlog reaches the log length
     const int per = (h->Nf + (h->H - 3)) / (h->H - 2);
     std::vector<std::pair<long long, int>> order;
@@ -1050,53 +1227,77 @@ extern "C" int slamgpu_resample(slamgpu_t *h, const double *unif, int32_t *keep_
     if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
     CU(cudaSetDevice(h->cfg.device));
     RET(flush_predicts(h));
+    UnifChoice uc = {false, 0};
     if (unif) {
         CU(cudaMemcpyAsync(h->unif(), unif, sizeof(double) * h->P, cudaMemcpyHostToDevice, h->stream));
     } else if (h->unif_inflight) {  // copied by slamgpu_update on the copy stream while the update kernel ran
         CU(cudaStreamWaitEvent(h->stream, h->ev_unif, 0));
         h->unif_inflight = false;
+        if (h->unif_is_ints) {  // raw rand() values: unifRand() = rand() / double(RAND_MAX), core.cpp:775-777
+            k_ints_to_unif<<<grid_for(h->P, 256), 256, 0, h->stream>>>(h->unif_i, h->unif(), h->P);
+            KCHECK();
+            LAUNCHED(h, SLAMGPU_T_WEIGHTS);
+            h->unif_is_ints = false;
+        }
     } else if (!h->unif_staged) {
-        return slam_fail(SLAMGPU_EINVAL, "resample needs unif[P] (or slamgpu_stage_noise first)");
+        if (!h->rng_on)
+            return slam_fail(SLAMGPU_EINVAL, "resample needs unif[P] (or slamgpu_stage_noise / slamgpu_seed first)");
+        uc.rng = true;
+        uc.draw = h->draw_resample++;
+    }
+    h->est_valid = false;
+    const size_t P = h->P;
+    if (h->dbg_capture) {
+        if (!h->dbg_w) CU(cudaMalloc(&h->dbg_w, sizeof(float) * 2 * P));
+        CU(cudaMemcpyAsync(h->dbg_w, h->w, sizeof(float) * P, cudaMemcpyDeviceToDevice, h->stream));
     }
     TimedSpan sp;
     RET(span_begin(h, SLAMGPU_T_WEIGHTS, &sp));
-    RET(resample_indices(h));
-    CU(cudaMemcpyAsync(h->h_sc, h->d_sc, sizeof(Scalars), cudaMemcpyDeviceToHost, h->stream));
+    RET(resample_indices(h, uc));
     RET(span_end(h, &sp));
+    if (h->dbg_capture) CU(cudaMemcpyAsync(h->dbg_w + P, h->w, sizeof(float) * P, cudaMemcpyDeviceToDevice, h->stream));
+    // The tail is enqueued BEFORE the host knows nEff: the pose gather and the pose estimate read the decision the
+    // weights kernel left on the device (Scalars::did), so the one read-back of the step overlaps them instead of
+    // sitting between two launches, and slamgpu_estimate right after an update costs neither a launch nor a second
+    // synchronisation.
+    const int *cond = h->cfg.do_resample ? &h->d_sc->did : nullptr;
+    if (cond) RET(launch_gather_pose(h, cond));
+    RET(launch_estimate(h, cond));
+    RET(fetch_tail(h));
     CU(cudaStreamSynchronize(h->stream));
-    if (h->h_sc->pad[0]) return slam_fail(SLAMGPU_ECOMM, "a peer device never arrived at an exchange (sharded resample)");
     h->gauss_chunked = false;
-    if (h->h_sc->gauss_late) {
-        cudaMemset(&h->d_sc->gauss_late, 0, sizeof(int));
-        return slam_fail(SLAMGPU_ECUDA, "the noise upload never arrived behind the update kernel");
-    }
-    if (h->h_sc->anomaly) {
-        // knife-edge ordering the search could not prove: run the exact sequential merge (core.cpp:800-806)
-        if (h->world > 1) return slam_fail(SLAMGPU_ECOMM, "sequential keep[] fallback is not available when sharded");
-        k_keep_sequential<<<1, 1, 0, h->stream>>>(h->sel, h->cdf, h->keep, h->P);
-        KCHECK();
-        LAUNCHED(h, SLAMGPU_T_WEIGHTS);
-    }
+    RET(report_device_flags(h));
     const float ne = h->h_sc->neff;
     const bool did = h->cfg.do_resample && (ne < (float) h->cfg.n_effective);  // core.cpp:739
+    if (did != (h->h_sc->did != 0)) return slam_fail(SLAMGPU_ECUDA, "internal: host and device disagree on the resample decision");
+    bool anomaly = false;
+    for (int r = 0; r < h->world; r++) anomaly = anomaly || h->h_tail[r].anomaly != 0;
+    if (anomaly) {
+        // knife-edge ordering the search could not prove (on some rank: the flags were exchanged with the tail records,
+        // so every rank takes this branch together): exact sequential merge, then the gather again with the exact keep[]
+        RET(keep_fallback(h));
+        if (did) RET(launch_gather_pose(h, nullptr));
+        h->stat_keep_fallbacks++;
+    } else {
+        combine_estimate(h);
+    }
     if (keep_out) {
         CU(cudaMemcpyAsync(keep_out, h->keep, sizeof(int) * h->P, cudaMemcpyDeviceToHost, h->stream));
         CU(cudaStreamSynchronize(h->stream));
     }
-    if (did) {
-        RET(resample_state(h));
-    }
+    if (did) RET(resample_commit(h));
     if (neff) *neff = ne;
     if (did_resample) *did_resample = did ? 1 : 0;
     return SLAMGPU_OK;
 }
 
-extern "C" int slamgpu_update(slamgpu_t *h, const float *zf, const int32_t *idf, int32_t K, const float *zn,
-                              int32_t Kn, const float R[4], const float *gauss, const double *unif,
-                              int32_t *did_resample, float *neff) {
+static int update_impl(slamgpu_t *h, const float *zf, const int32_t *idf, int32_t K, const float *zn, int32_t Kn,
+                       const float R[4], const float *gauss, const void *unif, bool unif_ints, int32_t *did_resample,
+                       float *neff) {
     if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
-    // Host noise goes up on a second stream: the 12 B/particle of Gaussians overlap the predict pass, the 8 B/particle
-    // of resample uniforms overlap the whole update kernel (they are first read by the search that follows it).
+    // Host noise goes up on a second stream: the 12 B/particle of Gaussians overlap the predict pass, the resample
+    // uniforms (8 B/particle as doubles, 4 B as raw rand() ints) overlap the whole update kernel (they are first read
+    // by the search that follows it).
     const bool want_gauss = gauss && h->cfg.method == SLAMGPU_FASTSLAM2 && (K > 0 || Kn > 0);
     if (want_gauss || unif) {
         CU(cudaSetDevice(h->cfg.device));
@@ -1115,13 +1316,16 @@ extern "C" int slamgpu_update(slamgpu_t *h, const float *zf, const int32_t *idf,
             if (chunked) {
                 // column chunks in particle order, each followed by its arrival flag: the update kernel's CTAs run in
                 // the same order and wait per chunk (kernels.cuh gauss_arrived_load), so only the first chunk's
-                // transfer is exposed instead of all 12 B x P
+                // transfer is exposed instead of all 12 B x P.  The flag is a 4-byte copy from a pinned constant: the
+                // copy engine writes it, in stream order behind the chunk — no SM slot is needed while every SM is full
+                // of waiting update CTAs (a cudaMemsetAsync is a kernel and would have to squeeze in between them).
                 const size_t C = (size_t) 1 << h->gauss_shift();
                 for (size_t c0 = 0, c = 0; c0 < h->P; c0 += C, c++) {
                     const size_t n = std::min(C, h->P - c0);
                     CU(cudaMemcpy2DAsync(h->gauss + c0, sizeof(float) * h->P, gauss + c0, sizeof(float) * h->P,
                                          sizeof(float) * n, 3, cudaMemcpyHostToDevice, h->copy_stream));
-                    CU(cudaMemsetAsync(h->gauss_flags + c, 0xff, sizeof(unsigned), h->copy_stream));
+                    CU(cudaMemcpyAsync(h->gauss_flags + c, h->h_ones, sizeof(unsigned), cudaMemcpyHostToDevice,
+                                       h->copy_stream));
                 }
             } else {
                 CU(cudaMemcpyAsync(h->gauss, gauss, sizeof(float) * 3 * h->P, cudaMemcpyHostToDevice, h->copy_stream));
@@ -1132,9 +1336,15 @@ extern "C" int slamgpu_update(slamgpu_t *h, const float *zf, const int32_t *idf,
             h->gauss_staged = false;
         }
         if (unif) {
-            CU(cudaMemcpyAsync(h->unif(), unif, sizeof(double) * h->P, cudaMemcpyHostToDevice, h->copy_stream));
+            if (unif_ints) {
+                if (!h->unif_i) CU(cudaMalloc(&h->unif_i, sizeof(int) * h->P));
+                CU(cudaMemcpyAsync(h->unif_i, unif, sizeof(int) * h->P, cudaMemcpyHostToDevice, h->copy_stream));
+            } else {
+                CU(cudaMemcpyAsync(h->unif(), unif, sizeof(double) * h->P, cudaMemcpyHostToDevice, h->copy_stream));
+            }
             CU(cudaEventRecord(h->ev_unif, h->copy_stream));
             h->unif_inflight = true;
+            h->unif_is_ints = unif_ints;
             h->unif_staged = false;
         }
     }
@@ -1145,6 +1355,27 @@ extern "C" int slamgpu_update(slamgpu_t *h, const float *zf, const int32_t *idf,
         h->gauss_inflight = h->unif_inflight = false;
     }
     return rc;
+}
+
+extern "C" int slamgpu_update(slamgpu_t *h, const float *zf, const int32_t *idf, int32_t K, const float *zn,
+                              int32_t Kn, const float R[4], const float *gauss, const double *unif,
+                              int32_t *did_resample, float *neff) {
+    return update_impl(h, zf, idf, K, zn, Kn, R, gauss, unif, false, did_resample, neff);
+}
+extern "C" int slamgpu_update_i32(slamgpu_t *h, const float *zf, const int32_t *idf, int32_t K, const float *zn,
+                                  int32_t Kn, const float R[4], const float *gauss, const int32_t *rand_ints,
+                                  int32_t *did_resample, float *neff) {
+    return update_impl(h, zf, idf, K, zn, Kn, R, gauss, rand_ints, true, did_resample, neff);
+}
+
+extern "C" int slamgpu_seed(slamgpu_t *h, uint64_t seed, int32_t predict_noise) {
+    if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
+    h->rng_on = true;
+    h->rng_predict_noise = predict_noise != 0;
+    h->rng_seed = seed;
+    h->draw_pose = h->draw_resample = h->draw_control = 0;
+    h->gauss_staged = h->unif_staged = false;  // staged host noise would take precedence
+    return SLAMGPU_OK;
 }
 
 // ---- computeJacobians ---------------------------------------------------------------------------------------
@@ -1225,42 +1456,64 @@ extern "C" int slamgpu_estimate(slamgpu_t *h, double *x, double *y, double *t) {
     if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
     CU(cudaSetDevice(h->cfg.device));
     RET(flush_predicts(h));
-    TimedSpan sp;
-    RET(span_begin(h, SLAMGPU_T_ESTIMATE, &sp));
-    PoseSoA s = h->soa(h->cur);
-    k_estimate<<<h->est_blocks, 256, 0, h->stream>>>(s.xv, s.w, h->P, (long long) h->slot0, h->d_est, h->est_ticket,
-                                                     h->d_est + h->est_blocks);
-    KCHECK();
-    LAUNCHED(h, SLAMGPU_T_ESTIMATE);
-    static_assert(sizeof(EstPartial) == 4 * SLAM_XCHG_BLOB_WORDS, "estimate record size");
-    if (h->world > 1) {
-        // every rank's partial lands in every rank's slab (peer stores, one exchange), then one read-back: no NCCL
-        // call, no second synchronisation.  Two landing areas by parity: a peer can be at most one exchange ahead.
-        const int slot = (int) (h->est_count++ & 1u);
-        RET(xchg(h, nullptr, 0, false, h->d_est + h->est_blocks, (int) sizeof(EstPartial), slot));
-        const float *area = h->tot_slab + 4 * h->nbg + (size_t) slot * SLAM_MAX_RANKS * SLAM_XCHG_BLOB_WORDS;
-        CU(cudaMemcpyAsync(h->h_est, area, sizeof(EstPartial) * h->world, cudaMemcpyDeviceToHost, h->stream));
-    } else {
-        CU(cudaMemcpyAsync(h->h_est, h->d_est + h->est_blocks, sizeof(EstPartial), cudaMemcpyDeviceToHost, h->stream));
+    if (!h->est_valid) {  // (right after an update the resample's tail has already produced it: no launch, no wait)
+        RET(launch_estimate(h, nullptr));
+        RET(fetch_tail(h));
+        CU(cudaStreamSynchronize(h->stream));
+        RET(report_device_flags(h));
+        combine_estimate(h);
     }
-    RET(span_end(h, &sp));
+    if (x) *x = h->est_x;
+    if (y) *y = h->est_y;
+    if (t) *t = h->est_t;
+    return SLAMGPU_OK;
+}
+
+// ---- parity instrumentation -----------------------------------------------------------------------------------------
+extern "C" int slamgpu_debug_capture(slamgpu_t *h, int32_t on) {
+    if (!h) return slam_fail(SLAMGPU_EINVAL, "null handle");
+    h->dbg_capture = on != 0;
+    return SLAMGPU_OK;
+}
+extern "C" int slamgpu_debug_read(slamgpu_t *h, int32_t which, void *out) {
+    if (!h || !out) return slam_fail(SLAMGPU_EINVAL, "null argument");
+    CU(cudaSetDevice(h->cfg.device));
+    const size_t P = h->P;
+    const void *src = nullptr;
+    size_t bytes = sizeof(float) * P;
+    switch (which) {
+        case SLAMGPU_DEBUG_W_BEFORE: src = h->dbg_w; break;
+        case SLAMGPU_DEBUG_W_NORMALISED: src = h->dbg_w ? h->dbg_w + P : nullptr; break;
+        case SLAMGPU_DEBUG_KEEP: src = h->keep; bytes = sizeof(int) * P; break;
+        case SLAMGPU_DEBUG_SELECT: src = h->sel; break;
+        default: return slam_fail(SLAMGPU_EINVAL, "unknown debug item");
+    }
+    if (!src) return slam_fail(SLAMGPU_EINVAL, "nothing captured (slamgpu_debug_capture, then a resample)");
+    CU(cudaMemcpyAsync(out, src, bytes, cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
-    double sx = h->h_est[0].sx, sy = h->h_est[0].sy, th = h->h_est[0].theta;
-    float best = h->h_est[0].wmax;
-    long long bi = h->h_est[0].imax;
-    for (int r = 1; r < h->world; r++) {  // rank order: identical result on every rank
-        const EstPartial &e = h->h_est[r];
-        sx += e.sx;
-        sy += e.sy;
-        if (e.wmax > best || (e.wmax == best && e.imax < bi)) {
-            best = e.wmax;
-            bi = e.imax;
-            th = e.theta;
-        }
+    return SLAMGPU_OK;
+}
+
+extern "C" int slamgpu_download_slice(slamgpu_t *h, int64_t p0, int64_t n, float *xv, float *Pv, float *w,
+                                      float *lm_mean, float *lm_cov) {
+    if (!h || p0 < 0 || n <= 0 || (size_t) (p0 + n) > h->P) return slam_fail(SLAMGPU_EINVAL, "slice outside [0, P)");
+    CU(cudaSetDevice(h->cfg.device));
+    RET(flush_predicts(h));
+    const size_t P = h->P, N = (size_t) n;
+    if (lm_mean || lm_cov) RET(materialise_all(h));
+    PoseSoA s = h->soa(h->cur);
+    const cudaMemcpyKind D2H = cudaMemcpyDeviceToHost;
+    if (xv) CU(cudaMemcpy2DAsync(xv, sizeof(float) * N, s.xv + p0, sizeof(float) * P, sizeof(float) * N, 3, D2H, h->stream));
+    if (Pv) CU(cudaMemcpy2DAsync(Pv, sizeof(float) * N, s.Pv + p0, sizeof(float) * P, sizeof(float) * N, 9, D2H, h->stream));
+    if (w) CU(cudaMemcpyAsync(w, s.w + p0, sizeof(float) * N, D2H, h->stream));
+    for (int l = 0; l < h->Nf; l++) {
+        const size_t row = (size_t) h->phys_row(l);
+        if (lm_mean)
+            CU(cudaMemcpyAsync(lm_mean + (size_t) l * N * 2, h->lm_mean + row * P + p0, sizeof(float2) * N, D2H, h->stream));
+        if (lm_cov)
+            CU(cudaMemcpyAsync(lm_cov + (size_t) l * N * 4, h->lm_cov + row * P + p0, sizeof(float4) * N, D2H, h->stream));
     }
-    if (x) *x = sx / (double) h->Pg;
-    if (y) *y = sy / (double) h->Pg;
-    if (t) *t = th;
+    CU(cudaStreamSynchronize(h->stream));
     return SLAMGPU_OK;
 }
 
@@ -1339,6 +1592,10 @@ extern "C" int slamgpu_comm_init(slamgpu_t *h, int32_t rank, int32_t world, cons
         return slam_fail(SLAMGPU_EINVAL, "sharded particle counts must be a multiple of 1024 per device");
     if (world > 1 && h->cfg.scan_mode != SLAMGPU_SCAN_BLOCKED)
         return slam_fail(SLAMGPU_EINVAL, "sharding needs SLAMGPU_SCAN_BLOCKED");
+    // keep[], the keep log and the ancestor maps are int32 GLOBAL indices and the upper scan level handles at most
+    // 1024 x 1024 block totals: the same bound slamgpu_create puts on one handle holds for the whole sharded set
+    if ((long long) h->P * (long long) world > (1ll << 30))
+        return slam_fail(SLAMGPU_EINVAL, "n_particles x world exceeds 2^30 (int32 global particle indices)");
     CU(cudaSetDevice(h->cfg.device));
     std::string err;
     SlamComm *c = comm_create(rank, world, id128, h->cfg.device, &err);

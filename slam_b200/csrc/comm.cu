@@ -7,8 +7,8 @@
 //   * particle migration is NOT a collective: every rank maps its peers' pose and landmark buffers (CUDA IPC over
 //     NVLink / NVSwitch) and the gather / update kernels (kernels.cuh K7, K3 REMAP) read particles[keep[i]] straight
 //     from the owning device, with a barrier between batches because freed physical rows are recycled;
-//   * NCCL remains for the bootstrap (the IPC handles travel in one all-gather), the all-gather of keep[] into the
-//     log (its own stream, off the critical path) and the SLAMGPU_XCHG_NCCL=1 A/B switch.  It is loaded at run time
+//   * NCCL remains for the bootstrap (the IPC handles travel in one all-gather) and the all-gather of keep[] into the
+//     log (its own stream, off the critical path).  It is loaded at run time
 //     from libnccl.so.2 (the copy torch already mapped when the caller is a torchrun rank, else the system one) so
 //     that a single-device build has no NCCL dependency.
 #include <dlfcn.h>
@@ -18,6 +18,7 @@
 #include <cstring>
 
 #include "handle.h"
+#include "xchg.cuh"
 
 using namespace slam;
 
@@ -28,10 +29,6 @@ struct NcclApi {
     decltype(&ncclCommInitRank) CommInitRank = nullptr;
     decltype(&ncclCommDestroy) CommDestroy = nullptr;
     decltype(&ncclAllGather) AllGather = nullptr;
-    decltype(&ncclSend) Send = nullptr;
-    decltype(&ncclRecv) Recv = nullptr;
-    decltype(&ncclGroupStart) GroupStart = nullptr;
-    decltype(&ncclGroupEnd) GroupEnd = nullptr;
     decltype(&ncclGetErrorString) GetErrorString = nullptr;
 };
 
@@ -48,8 +45,7 @@ static int load_nccl(NcclApi *api, std::string *err) {
         *err = "libnccl.so.2 lacks nccl" #name;                                \
         return -1;                                                             \
     }
-    SYM(GetUniqueId) SYM(CommInitRank) SYM(CommDestroy) SYM(AllGather) SYM(Send) SYM(Recv) SYM(GroupStart)
-    SYM(GroupEnd) SYM(GetErrorString)
+    SYM(GetUniqueId) SYM(CommInitRank) SYM(CommDestroy) SYM(AllGather) SYM(GetErrorString)
 #undef SYM
     api->lib = lib;
     return 0;
@@ -130,13 +126,6 @@ void comm_destroy(SlamComm *c) {
 
 
 
-static int barrier(SlamComm *c, cudaStream_t st) {
-    // stream-ordered: completes on a rank only once every rank's stream has reached it
-    float *b = (float *) (c->d_small + 6144);
-    NC(g_nccl.AllGather(b + c->rank, b, 1, ncclFloat32, c->comm, st));
-    return SLAMGPU_OK;
-}
-
 static int open_peers(SlamComm *c, slamgpu *h) {
     if (c->peers_open) return SLAMGPU_OK;
     cudaIpcMemHandle_t mine[9];
@@ -182,70 +171,13 @@ int comm_peer_maps(SlamComm *c, slamgpu *h, PeerMaps *out) {
 }
 
 
-// ---- small exchanges over peer memory --------------------------------------------------------------------------------
-// The sharded resample needs three tiny all-gathers (<= 4 KB per rank) and a few barriers per update.  Through NCCL each
-// costs a launch plus ~20 us of protocol at 8 devices; here one 1-CTA kernel per rank STORES its chunk straight into
-// every peer's copy of the array over NVLink (the buffers are CUDA-IPC mapped), publishes an arrival counter in every
-// peer's flag array with a system-scope fence, and spins on its own flags until all peers have arrived: the stores of a
-// peer are visible once its counter is.  Every rank issues the same sequence of exchanges, so the counter is simply the
-// exchange number.  A chunk is rewritten only after at least one later exchange (= barrier) that follows its last
-// reader in stream order, see capi.cu resample_indices.  The wait is bounded (~20 s of SM clocks): a missing peer
-// raises *error, which the host turns into SLAMGPU_ECOMM, instead of hanging the device.
-__global__ void __launch_bounds__(256) k_xchg(const XchgArgs a) {
-    const int tid = threadIdx.x;
-    for (int k = 0; k < a.narr; k++) {
-        const float *src = a.slab[a.rank] + a.arr_off[k] + a.b0;
-        for (int r = 0; r < a.world; r++) {
-            if (r == a.rank) continue;
-            float *dst = a.slab[r] + a.arr_off[k] + a.b0;
-            for (int i = tid; i < a.count; i += blockDim.x) dst[i] = src[i];
-        }
-    }
-    if (a.blob_words && tid < a.blob_words * a.world) {
-        const int r = tid / a.blob_words, k = tid % a.blob_words;
-        reinterpret_cast<unsigned *>(a.slab[r])[a.blob_off + a.rank * a.blob_words + k] = a.blob_src[k];
-    }
-    if (a.halo && a.rank + 1 < a.world && tid < 2)  // the next rank's search needs this rank's last two uniforms
-        a.unif[a.rank + 1][tid] = a.unif[a.rank][a.P + tid];
-    __threadfence_system();
-    __syncthreads();
-    if (tid < a.world) {
-        __threadfence_system();  // cumulative: the whole CTA's stores (ordered by the barrier) precede the counter
-        volatile unsigned long long *theirs = a.flags[tid] + a.rank;
-        *theirs = a.epoch;
-        volatile unsigned long long *mine = a.flags[a.rank] + tid;
-        const long long t0 = clock64();
-        while (*mine < a.epoch) {
-            if (clock64() - t0 > 40000000000ll) {
-                *a.error = 1;
-                break;
-            }
-        }
-    }
-    __threadfence_system();
-    __syncthreads();
-}
+// ---- small exchanges over peer memory (xchg.cuh) ---------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_xchg(const XchgArgs a) { xchg_body(a); }
 
-int comm_exchange(SlamComm *c, slamgpu *h, const int *arrays, int narr, bool halo, const void *blob, int blob_bytes,
-                  int blob_slot) {
+int comm_fill_xchg(SlamComm *c, slamgpu *h, const int *arrays, int narr, bool halo, const void *blob, int blob_bytes,
+                   int blob_slot, XchgArgs *out) {
     RET(open_peers(c, h));
-    static const bool via_nccl = getenv("SLAMGPU_XCHG_NCCL") != nullptr;  // A/B switch: the same exchanges through NCCL
-    if (via_nccl && !blob) {  // (the estimate record always goes by peer memory)
-        if (narr == 0 && !halo) return barrier(c, h->stream);
-        NC(g_nccl.GroupStart());
-        for (int k = 0; k < narr; k++) {
-            float *buf = h->tot_slab + (size_t) arrays[k] * h->nbg;
-            NC(g_nccl.AllGather(buf + (size_t) c->rank * h->nb, buf, h->nb, ncclFloat32, c->comm, h->stream));
-        }
-        if (halo) {
-            if (c->rank + 1 < c->world)
-                NC(g_nccl.Send(h->unif_base + h->P, 2, ncclFloat64, c->rank + 1, c->comm, h->stream));
-            if (c->rank > 0) NC(g_nccl.Recv(h->unif_base, 2, ncclFloat64, c->rank - 1, c->comm, h->stream));
-        }
-        NC(g_nccl.GroupEnd());
-        return SLAMGPU_OK;
-    }
-    XchgArgs a;
+    XchgArgs &a = *out;
     memset(&a, 0, sizeof(a));
     for (int r = 0; r < c->world; r++) {
         a.slab[r] = c->peers.slab[r];
@@ -261,12 +193,19 @@ int comm_exchange(SlamComm *c, slamgpu *h, const int *arrays, int narr, bool hal
     a.count = (int) h->nb;
     a.halo = halo ? 1 : 0;
     a.P = h->P;
-    a.error = &h->d_sc->pad[0];
+    a.error = &h->d_sc->comm_error;
     if (blob) {
         a.blob_src = (const unsigned *) blob;
         a.blob_words = blob_bytes / 4;
-        a.blob_off = 4 * (int) h->nbg + blob_slot * SLAM_MAX_RANKS * SLAM_XCHG_BLOB_WORDS;
+        a.blob_off = (int) SLAM_BLOB_BASE(h->nbg) + blob_slot * SLAM_MAX_RANKS * SLAM_XCHG_BLOB_WORDS;
     }
+    return SLAMGPU_OK;
+}
+
+int comm_exchange(SlamComm *c, slamgpu *h, const int *arrays, int narr, bool halo, const void *blob, int blob_bytes,
+                  int blob_slot) {
+    XchgArgs a;
+    RET(comm_fill_xchg(c, h, arrays, narr, halo, blob, blob_bytes, blob_slot, &a));
     k_xchg<<<1, 256, 0, h->stream>>>(a);
     if (cudaGetLastError() != cudaSuccess) return slam_fail(SLAMGPU_ECOMM, "peer-memory exchange launch failed");
     h->launches++;

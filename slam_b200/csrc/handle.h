@@ -33,13 +33,8 @@ using slam::PoseSoA;
 
 #define SLAM_OBS_SLOTS 4  // rotating pinned staging slots for the observation set
 
-struct Scalars {  // device + pinned mirror
-    float ws, s2, csum, neff;
-    int anomaly;
-    int pad[3];      // [0] peer-exchange time-out; [1..2] 64-bit count of remote resample sources
-    int gauss_late;  // a chunk of an in-flight noise upload never arrived (GaussArrival); cleared by the host on error
-    int pad2[3];
-};
+using slam::Scalars;   // device scalars of the resample + pinned mirror (types.cuh)
+using slam::TailBlob;  // pose-estimate partial + anomaly flag a resample's tail leaves for the host
 
 struct TimedSpan {
     cudaEvent_t a, b;
@@ -71,7 +66,7 @@ struct slamgpu {
     slam::RowPair *d_pairs = nullptr, *h_pairs = nullptr;  // row-move lists (device / pinned), nf_cap entries
     int *d_phys = nullptr;       // device copy of phys[] for the download helpers
     std::vector<slam::PredictArgs> predict_queue;  // noise-free predict ticks not yet applied (flush_predicts)
-    int64_t stat_rows_moved = 0, stat_resamples = 0, stat_chain_steps = 0, stat_rows_fused = 0;
+    int64_t stat_rows_moved = 0, stat_resamples = 0, stat_chain_steps = 0, stat_rows_fused = 0, stat_keep_fallbacks = 0;
     cudaStream_t stream = nullptr, own_stream = nullptr;
     float *pose[2] = {nullptr, nullptr};  // each: xv[3][P] then Pv[9][P]
     int cur = 0;
@@ -84,8 +79,12 @@ struct slamgpu {
     float *cdf = nullptr, *mloc = nullptr;  // [Pg]
     float *sel = nullptr;        // [P]
     int *keep = nullptr;         // [P]
-    float *tot_slab = nullptr;   // [4][nb_global]: the four arrays below, one allocation (one peer mapping)
-    float *tot_w = nullptr, *tot_c = nullptr, *tot_s = nullptr, *bmax = nullptr;  // [nb_global] each
+    float *tot_slab = nullptr;   // [SLAM_SLAB_ARRAYS][nb_global]: the arrays below, one allocation (one peer mapping)
+    float *tot_w = nullptr, *tot_c = nullptr, *tot_s = nullptr, *lmax = nullptr, *bm = nullptr;  // [nb_global] each
+    unsigned *gbar = nullptr;    // grid-barrier counter of the cooperative weights kernel (only ever grows)
+    unsigned gbar_base = 0;      // its value before the next launch
+    int coop_grid = 0;           // CTAs of the cooperative launch (0: split launches, SLAMGPU_WEIGHTS_SPLIT / unsupported)
+    bool force_anomaly = false;  // SLAMGPU_FORCE_ANOMALY: every search reports an unproven slot (exercises the fallback)
     unsigned long long *xflags = nullptr;  // [SLAM_MAX_RANKS] arrival counters written by the peers (comm.cu k_xchg)
     size_t nb = 0, nbg = 0;      // local / global 1024-blocks
     Scalars *d_sc = nullptr, *h_sc = nullptr;
@@ -96,8 +95,24 @@ struct slamgpu {
     size_t rec_cap = 0;
     int obs_cap = 0;
     void *h_obs = nullptr;       // pinned staging for the observation set
-    EstPartial *d_est = nullptr, *h_est = nullptr;
+    EstPartial *d_est = nullptr;  // per-CTA partials of k_estimate
+    TailBlob *d_tail = nullptr, *h_tail = nullptr;  // device record / pinned [SLAM_MAX_RANKS] (one per rank when sharded)
+    TailBlob *d_chain = nullptr;  // record of the sharded keep[] fallback: where this rank's sequential merge ended
     int est_blocks = 0;
+    // the estimate a resample's tail has already produced (slamgpu_estimate returns it without a launch); dropped by
+    // anything that moves the poses
+    bool est_valid = false;
+    double est_x = 0, est_y = 0, est_t = 0;
+    // throughput mode: noise from the device generator (slam_rng.cuh) instead of host buffers
+    bool rng_on = false, rng_predict_noise = false;
+    unsigned long long rng_seed = 0;
+    unsigned draw_pose = 0, draw_resample = 0, draw_control = 0;
+    // parity instrumentation (slamgpu_debug_capture): weights before / after normalisation of the last resample
+    bool dbg_capture = false;
+    float *dbg_w = nullptr;       // [2][P]
+    int *unif_i = nullptr;        // [P] raw rand() ints of slamgpu_update_i32 (converted on the device)
+    bool unif_is_ints = false;
+    unsigned *h_ones = nullptr;   // pinned constant: arrival flags are written by the copy engine, not by a kernel
     bool gauss_staged = false, unif_staged = false;
     // slamgpu_update's host noise travels on a second stream (capi.cu)
     cudaStream_t copy_stream = nullptr;
@@ -110,7 +125,7 @@ struct slamgpu {
     bool gauss_chunked = false;       // the in-flight Gaussians carry per-chunk arrival flags (types.cuh GaussArrival)
     unsigned *gauss_flags = nullptr;  // [SLAM_GAUSS_CHUNKS]
     unsigned *est_ticket = nullptr;   // k_estimate's last-CTA counter (self-resetting)
-    unsigned est_count = 0;           // sharded: parity selects one of two landing areas for the peers' partials
+    unsigned tail_count = 0;          // sharded: parity selects one of two landing areas for the peers' tail records
     int gauss_rows_staged = 0;
     // timing
     bool timing = false;
@@ -154,9 +169,13 @@ void comm_destroy(SlamComm *c);
 // Maps every peer's pose / landmark buffers (CUDA IPC, once) and returns the table the gather kernels index by rank.
 int comm_peer_maps(SlamComm *c, slamgpu *h, PeerMaps *out);
 // Small exchange over peer memory instead of NCCL (latency: one 1-CTA kernel): all-gathers this rank's chunk
-// [b0, b0 + nb) of the listed block-total arrays (0 tot_w, 1 tot_c, 2 tot_s, 3 bmax), optionally sends the uniform
-// halo to the next rank, optionally pushes a small record (blob) into one of two landing areas of every rank, and
+// [b0, b0 + nb) of the listed block-total arrays (0 tot_w, 1 tot_c, 2 tot_s, 3 lmax), optionally sends the uniform
+// halo to the next rank, optionally pushes a small record (blob) into one of the landing areas of every rank, and
 // is a stream-ordered barrier over all ranks.  narr == 0 and no blob: barrier only.
+// comm_fill_xchg prepares the arguments (and consumes one exchange number) without launching: the cooperative weights
+// kernel runs the exchange itself (xchg.cuh); comm_exchange = fill + launch of the stand-alone kernel.
+int comm_fill_xchg(SlamComm *c, slamgpu *h, const int *arrays, int narr, bool halo, const void *blob, int blob_bytes,
+                   int blob_slot, slam::XchgArgs *out);
 int comm_exchange(SlamComm *c, slamgpu *h, const int *arrays, int narr, bool halo, const void *blob = nullptr,
                   int blob_bytes = 0, int blob_slot = 0);
 // In-place NCCL all-gather over a global int array (the keep log): this rank's count elements sit at buf + rank*count.

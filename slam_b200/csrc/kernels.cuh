@@ -13,7 +13,9 @@
 #include <stdint.h>
 
 #include "slam_math.cuh"
+#include "slam_rng.cuh"
 #include "types.cuh"
+#include "xchg.cuh"
 
 namespace slam {
 
@@ -36,21 +38,20 @@ __device__ __forceinline__ void store_pose(const PoseSoA &s, size_t P, size_t p,
 
 // ---------------------------------------------------------------------------------------------------------
 // K1  predict: FastSLAM{1,2}::predict over all particles (fastslam2.cpp:51-60, fastslam1.cpp:57-66).
-// gauss: nullptr or [2][P] standard normals.  96 B of state traffic per particle (FastSLAM2).
+// noise: [2][P] staged standard normals or the device generator (slam_rng.cuh).  96 B of state traffic per particle
+// (FastSLAM2).
 // ---------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_predict(PoseSoA s, size_t P, PredictArgs a, const float *__restrict__ gauss) {
+__global__ void __launch_bounds__(256) k_predict(PoseSoA s, size_t P, PredictArgs a, const NoiseSrc noise) {
     const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= P) return;
     const bool need_cov = (a.method == 2) || a.use_heading;
     float x[3], C[9];
     load_pose(s, P, p, x, need_cov ? C : nullptr);
     float g2[2];
-    if (gauss) {
-        g2[0] = gauss[p];
-        g2[1] = gauss[P + p];
-    }
+    const bool noisy = noise.rng || noise.gauss;
+    if (noisy) noise_gauss2(noise, P, p, g2);
     predict_particle(a.method, x, C, a.V, a.G, a.Q, a.dt, a.phi_true, a.wheel_base, a.sigma_phi, a.use_heading != 0,
-                     gauss ? g2 : nullptr);
+                     noisy ? g2 : nullptr);
     store_pose(s, P, p, x, need_cov ? C : nullptr);
 }
 
@@ -129,7 +130,7 @@ __device__ __forceinline__ void stage_obs(const ObsSet &o, int K, float2 *&sz, i
 }
 
 __global__ void __launch_bounds__(128) k_fs2_update(PoseSoA s, MapRing m, size_t P, ObsSet o, int K, float4 Rm,
-                                                    const float *__restrict__ gauss) {
+                                                    const NoiseSrc noise) {
     float2 *sz;
     int *srow;
     stage_obs(o, K, sz, srow);
@@ -142,7 +143,8 @@ __global__ void __launch_bounds__(128) k_fs2_update(PoseSoA s, MapRing m, size_t
     for (int j = 0; j < 3; j++) x0[j] = x[j];
 #pragma unroll
     for (int j = 0; j < 9; j++) C0[j] = C[j];
-    const float g3[3] = {gauss[p], gauss[P + p], gauss[2 * P + p]};
+    float g3[3];
+    noise_gauss3(noise, P, p, g3);
     float wgt = s.w[p];
 
     // pass 1: proposal, sequential over observations, next landmark prefetched while this one is processed
@@ -199,13 +201,14 @@ __device__ __forceinline__ void fs2_update_particle_reference_order(PoseSoA s, M
                                                                     const float2 *sz, const unsigned long long *soff,
                                                                     const unsigned long long *doff,
                                                                     const float2 *smean, const float4 *scov,
-                                                                    int K, float4 Rm, const float *gauss) {
+                                                                    int K, float4 Rm, const NoiseSrc &noise) {
     const float R[4] = {Rm.x, Rm.y, Rm.z, Rm.w};
     float x[3], C[9], x0[3], C0[9];
     load_pose(s, P, p, x, C);
     for (int j = 0; j < 3; j++) x0[j] = x[j];
     for (int j = 0; j < 9; j++) C0[j] = C[j];
-    const float g3[3] = {gauss[p], gauss[P + p], gauss[2 * P + p]};
+    float g3[3];
+    noise_gauss3(noise, P, p, g3);
     float xf[2], Pf[4];
     for (int i = 0; i < K; i++) {
         const bool stale = REMAP && soff[i] != doff[i];
@@ -293,7 +296,7 @@ __device__ __forceinline__ unsigned spread_block(unsigned b, unsigned nblocks, u
 
 template <bool REMAP>
 __global__ void __launch_bounds__(128) k_fs2_update_listed(PoseSoA s, MapRing m, size_t P, ObsSet o, int K, float4 Rm,
-                                                           const float *__restrict__ gauss,
+                                                           const NoiseSrc noise,
                                                            const int *__restrict__ anc, PeerRows pr, long long n_global,
                                                            const int *__restrict__ list, const int *__restrict__ count) {
     float2 *sz;
@@ -305,7 +308,7 @@ __global__ void __launch_bounds__(128) k_fs2_update_listed(PoseSoA s, MapRing m,
         const float2 *smean = nullptr;
         const float4 *scov = nullptr;
         if (REMAP) remap_source(pr, remap_column(anc, p, n_global), P, smean, scov);
-        fs2_update_particle_reference_order<REMAP>(s, m, P, p, sz, soff, doff, smean, scov, K, Rm, gauss);
+        fs2_update_particle_reference_order<REMAP>(s, m, P, p, sz, soff, doff, smean, scov, K, Rm, noise);
     }
 }
 
@@ -339,16 +342,21 @@ __device__ __forceinline__ void cp_async_wait() {
 // write of 24 B per particle-landmark saved on every update that follows a resample).
 // Waits until this warp's chunk of a noise buffer that is still being uploaded has landed (GaussArrival), then reads
 // the thread's three Gaussians with loads the compiler cannot move above the wait.
-__device__ __forceinline__ void gauss_arrived_load(const GaussArrival &ga, const float *gauss, size_t P, size_t p,
+__device__ __forceinline__ void gauss_arrived_load(const GaussArrival &ga, const NoiseSrc &noise, size_t P, size_t p,
                                                    float g3[3]) {
-    if (ga.flags) {
+    const float *gauss = noise.gauss;
+    if (noise.rng) {
+        rng_gauss3(noise.seed, noise.slot0 + p, noise.draw, g3);
+    } else if (ga.flags) {
         const unsigned am = __activemask();  // lanes that left for the fallback list are not here
         if ((int) (threadIdx.x & 31) == __ffs(am) - 1) {
             const unsigned *f = ga.flags + (p >> ga.shift);
             unsigned v;
             const long long t0 = clock64();
             while (true) {
-                asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+                // acquire at system scope: the flag is written by the copy engine behind the chunk it announces, and the
+                // data loads below must observe what that write follows
+                asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
                 if (v) break;
                 if (clock64() - t0 > 4000000000ll) {  // ~2 s: the copy stream died
                     *ga.late = 1;
@@ -370,7 +378,7 @@ __device__ __forceinline__ void gauss_arrived_load(const GaussArrival &ga, const
 
 template <bool REMAP>
 __global__ void __launch_bounds__(SLAM_UPDATE_THREADS, 7) k_fs2_update_fast(PoseSoA s, MapRing m, size_t P, ObsSet o, int K,
-                                                                         float4 Rm, const float *gauss, GaussArrival ga,
+                                                                         float4 Rm, const NoiseSrc noise, GaussArrival ga,
                                                                          const int *__restrict__ anc, PeerRows pr,
                                                                          long long n_global,
                                                                          int *__restrict__ list, int *__restrict__ count) {
@@ -433,7 +441,7 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS, 7) k_fs2_update_fast(Pose
         }
     }
     float g3[3];
-    gauss_arrived_load(ga, gauss, P, p, g3);
+    gauss_arrived_load(ga, noise, P, p, g3);
     float xs[3];
     const float ratio = proposal_finish_fast(x0, L0, x, pi, g3, xs);
 
@@ -540,7 +548,7 @@ __global__ void __launch_bounds__(256) k_fs1_update(PoseSoA s, MapRing m, size_t
 // FastSLAM2's "no known landmark this step" branch (fastslam2.cpp:36-42): xv ~ N(xv, Pv), Pv = 0 first.
 // ---------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_add_feature(PoseSoA s, MapRing m, size_t P, ObsSet o, int Kn, float4 Rm,
-                                                     int sample_first, const float *__restrict__ gauss) {
+                                                     int sample_first, const NoiseSrc noise) {
     float2 *sz;
     int *srow;
     stage_obs(o, Kn, sz, srow);
@@ -551,7 +559,8 @@ __global__ void __launch_bounds__(256) k_add_feature(PoseSoA s, MapRing m, size_
     if (sample_first) {
         float C[9], xs[3];
         load_pose(s, P, p, x, C);
-        const float g3[3] = {gauss[p], gauss[P + p], gauss[2 * P + p]};
+        float g3[3];
+        noise_gauss3(noise, P, p, g3);
         multivariate_gauss<3>(x, C, g3, xs);
         const float Z[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
         store_pose(s, P, p, xs, Z);
@@ -658,110 +667,224 @@ __device__ __forceinline__ float block_maxscan_1024(float v, float *sh) {
     return (wid > 0) ? fmaxf(sh[wid - 1], loc) : loc;
 }
 
-// Step A: per-block totals of w.  tot[b] = last live element of the block's local scan.
-__global__ void __launch_bounds__(SLAM_SCAN_BLOCK) k_block_totals(const float *__restrict__ w, size_t n,
-                                                                  float *__restrict__ tot) {
-    __shared__ float sh[32];
-    const size_t i = (size_t) blockIdx.x * SLAM_SCAN_BLOCK + threadIdx.x;
-    const float v = (i < n) ? w[i] : 0.0f;
+// ---- the blocked weights pass: Sigma w -> normalise -> in-block CDF -> block totals -> nEff, block maxima --------------
+//
+// One pass structure shared by the cooperative kernel (k_weights_fused: ONE launch, two grid-wide barriers, the
+// cross-rank exchanges done by CTA 0 inside the barriers) and by the split launches (k_weights_a / _c / _d with
+// k_xchg in between; SLAMGPU_WEIGHTS_SPLIT=1, same device functions, same bits):
+//   A  per 1024-block scan of w                         -> tot_w[b]                       | exchange tot_w
+//   B  every CTA: ws = blocked total of tot_w (the recursion's upper levels, read only)
+//   C  wn = w / ws (one IEEE divide, stored back), in-block scans of wn and wn^2, running maximum of the in-block
+//      CDF                                              -> cdf_loc, mloc_loc, tot_c, tot_s, lmax | exchange those
+//   D  CTA 0: Tc = blocked scan of tot_c (in place), bm[b] = prefix max of fl(Tc[b-1] + lmax[b]);
+//      CTA 1: nEff = 1 / blocked total of tot_s, and the resample decision of core.cpp:739
+// The final CDF fl(Tc[b-1] + cdf_loc[i]) is never stored: rounding is monotone, so the running maximum of the final
+// CDF inside a block is fl(Tc[b-1] + mloc_loc[i]) and the block's maximum is fl(Tc[b-1] + lmax[b]) — the search adds
+// the block prefix to the in-block values it probes.  What a peer has to see of this device is therefore complete
+// after the SECOND exchange: the third exchange (and its barrier) of the earlier version is gone.
+struct WeightsArgs {
+    float *w;
+    size_t n;                              // particles on this device
+    float *tot_w, *tot_c, *tot_s, *lmax;   // [nbg] each, indexed by GLOBAL block (the slab every rank holds whole)
+    float *bm;                             // [nbg] out: prefix maxima of the block maxima of the final CDF
+    float *cdf_loc, *mloc_loc;             // [n] out: in-block CDF of the normalised weights, its running maximum
+    int b0;                                // first global block held here
+    int nb, nbg;                           // local / global 1024-blocks
+    Scalars *sc;
+    float neff_threshold;                  // (float) NEFFECTIVE
+    int do_resample;
+};
+
+__device__ __forceinline__ void weights_phase_a(const WeightsArgs &a, int lb, float *sh) {
+    const size_t i = (size_t) lb * SLAM_SCAN_BLOCK + threadIdx.x;
+    const float v = (i < a.n) ? a.w[i] : 0.0f;
     const float sc = block_scan_1024(v, sh);
-    const size_t last = min(n, ((size_t) blockIdx.x + 1) * SLAM_SCAN_BLOCK) - 1;
-    if (i == last) tot[blockIdx.x] = sc;
+    const size_t last = min(a.n, ((size_t) lb + 1) * SLAM_SCAN_BLOCK) - 1;
+    if (i == last) a.tot_w[a.b0 + lb] = sc;
 }
 
-// Steps B/D: the recursive part of the blocked scan over a totals array, by ONE CTA of 1024 threads, in place.
-// Handles n <= 1024*1024 totals (P <= 2^30): chunks of 1024 are scanned locally one after the other, the chunk
-// totals are scanned as one block (that is the recursion's last level), and added back.
-// blockIdx.x selects one of up to 3 independent arrays.  sum_out[blockIdx.x] = blocked_sum of the level below.
-struct UpperArgs {
-    float *arr[3];
-    float *sum_out[3];
-    float *recip_out[3];  // nullable: 1 / sum as one IEEE divide (nEff = 1 / sum(w^2), core.cpp:788-791)
-    int n;
-    int use_max;  // 1: max-scan (exact, order free) instead of the add scan
-};
-__global__ void __launch_bounds__(SLAM_SCAN_BLOCK) k_scan_upper(UpperArgs a) {
-    __shared__ float sh[32];
-    __shared__ float chunk_tot[SLAM_SCAN_BLOCK];
-    float *x = a.arr[blockIdx.x];
-    const int n = a.n;
+// Normalise (core.cpp:727-729 / 784-786: one quotient serves both), in-block CDF, totals of wn and wn^2.
+// pow(w,2) is a double product stored as float == one correctly rounded fp32 multiply.
+__device__ __forceinline__ void weights_phase_c(const WeightsArgs &a, int lb, float ws, float *sh) {
+    const size_t i = (size_t) lb * SLAM_SCAN_BLOCK + threadIdx.x;
+    float wn = 0.0f;
+    if (i < a.n) {
+        wn = __fdiv_rn(a.w[i], ws);
+        a.w[i] = wn;
+    }
+    const float sq = __fmul_rn(wn, wn);
+    const float sc = block_scan_1024(wn, sh);
+    const float ss = block_scan_1024(sq, sh);
+    const float mx = block_maxscan_1024((i < a.n) ? sc : -INFINITY, sh);
+    if (i < a.n) {
+        a.cdf_loc[i] = sc;
+        a.mloc_loc[i] = mx;
+    }
+    const size_t last = min(a.n, ((size_t) lb + 1) * SLAM_SCAN_BLOCK) - 1;
+    if (i == last) {
+        a.tot_c[a.b0 + lb] = sc;
+        a.tot_s[a.b0 + lb] = ss;
+        a.lmax[a.b0 + lb] = mx;
+    }
+}
+
+// The upper levels of the blocked scan over a totals array x[n], n <= 1024 * 1024, by ONE CTA of 1024 threads:
+// chunks of 1024 are scanned one after the other, the chunk totals are scanned as one block (the recursion's last
+// level) and added back.  The slab arrays are written by other CTAs / other devices: read through L2 (ld.cg).
+// upper_total: read only; returns the blocked SUM of the level below = scanned[n-2] + x[n-1] to every thread.
+__device__ __forceinline__ float upper_total(const float *x, int n, float *sh, float *chunk_tot, float *bcast) {
+    __syncthreads();  // bcast / chunk_tot may still be read from a previous call
+    if (n == 1) {
+        if (threadIdx.x == 0) *bcast = __ldcg(x);
+        __syncthreads();
+        return *bcast;
+    }
+    const int e = n - 2, ce = e / SLAM_SCAN_BLOCK, oe = e % SLAM_SCAN_BLOCK;
+    for (int c = 0; c <= ce; c++) {
+        const int i = c * SLAM_SCAN_BLOCK + threadIdx.x;
+        const float v = (i < n) ? __ldcg(x + i) : 0.0f;
+        const float sc = block_scan_1024(v, sh);
+        const int last = min(n, (c + 1) * SLAM_SCAN_BLOCK) - 1;
+        if (i == last) chunk_tot[c] = sc;
+        if (c == ce && (int) threadIdx.x == oe) *bcast = sc;
+    }
+    __syncthreads();
+    if (ce > 0) {
+        const float v = ((int) threadIdx.x < ce) ? chunk_tot[threadIdx.x] : 0.0f;  // chunks 0 .. ce-1 precede element e
+        const float sc = block_scan_1024(v, sh);
+        if ((int) threadIdx.x == ce - 1) *bcast = __fadd_rn(sc, *bcast);
+        __syncthreads();
+    }
+    return __fadd_rn(*bcast, __ldcg(x + n - 1));
+}
+// upper_scan_inplace: x[i] <- blocked inclusive scan (add, or max); returns nothing.
+__device__ __forceinline__ void upper_scan_inplace(float *x, int n, bool use_max, float *sh, float *chunk_tot) {
     const int nchunk = (n + SLAM_SCAN_BLOCK - 1) / SLAM_SCAN_BLOCK;
-    // the SUM of the level below is the last element of ITS scan = scanned[n-2] + (unscanned) x[n-1]
-    const float orig_last = (threadIdx.x == 0) ? x[n - 1] : 0.0f;
+    __syncthreads();
     for (int c = 0; c < nchunk; c++) {
         const int i = c * SLAM_SCAN_BLOCK + threadIdx.x;
-        const float v = (i < n) ? x[i] : (a.use_max ? -INFINITY : 0.0f);
-        const float sc = a.use_max ? block_maxscan_1024(v, sh) : block_scan_1024(v, sh);
-        if (i < n) x[i] = sc;
+        const float v = (i < n) ? __ldcg(x + i) : (use_max ? -INFINITY : 0.0f);
+        const float sc = use_max ? block_maxscan_1024(v, sh) : block_scan_1024(v, sh);
+        if (i < n) __stcg(x + i, sc);
         const int last = min(n, (c + 1) * SLAM_SCAN_BLOCK) - 1;
         if (i == last) chunk_tot[c] = sc;
     }
     __syncthreads();
     if (nchunk > 1) {
-        const float v = ((int) threadIdx.x < nchunk) ? chunk_tot[threadIdx.x] : (a.use_max ? -INFINITY : 0.0f);
-        const float sc = a.use_max ? block_maxscan_1024(v, sh) : block_scan_1024(v, sh);
+        const float v = ((int) threadIdx.x < nchunk) ? chunk_tot[threadIdx.x] : (use_max ? -INFINITY : 0.0f);
+        const float sc = use_max ? block_maxscan_1024(v, sh) : block_scan_1024(v, sh);
         __syncthreads();
         if ((int) threadIdx.x < nchunk) chunk_tot[threadIdx.x] = sc;
         __syncthreads();
         for (int c = 1; c < nchunk; c++) {
             const int i = c * SLAM_SCAN_BLOCK + threadIdx.x;
-            if (i < n) x[i] = a.use_max ? fmaxf(chunk_tot[c - 1], x[i]) : __fadd_rn(chunk_tot[c - 1], x[i]);
+            if (i < n) {
+                const float xi = __ldcg(x + i);
+                __stcg(x + i, use_max ? fmaxf(chunk_tot[c - 1], xi) : __fadd_rn(chunk_tot[c - 1], xi));
+            }
         }
     }
     __syncthreads();
-    if (threadIdx.x == 0 && a.sum_out[blockIdx.x]) {
-        const float total = (n > 1) ? __fadd_rn(x[n - 2], orig_last) : orig_last;
-        *a.sum_out[blockIdx.x] = total;
-        if (a.recip_out[blockIdx.x]) *a.recip_out[blockIdx.x] = __fdiv_rn(1.0f, total);
+}
+
+// Phase D.  which == 0: the CDF side (Tc in place, csum, bm); which == 1: nEff and the decision.
+__device__ __forceinline__ void weights_phase_d(const WeightsArgs &a, int which, float ws, float *sh, float *chunk_tot,
+                                                float *bcast) {
+    const int n = a.nbg;
+    if (which == 0) {
+        const float csum = upper_total(a.tot_c, n, sh, chunk_tot, bcast);  // before the scan overwrites the totals
+        upper_scan_inplace(a.tot_c, n, false, sh, chunk_tot);
+        for (int b = threadIdx.x; b < n; b += blockDim.x) {
+            const float l = __ldcg(a.lmax + b);
+            __stcg(a.bm + b, b > 0 ? __fadd_rn(__ldcg(a.tot_c + b - 1), l) : l);
+        }
+        upper_scan_inplace(a.bm, n, true, sh, chunk_tot);
+        if (threadIdx.x == 0) {
+            a.sc->ws = ws;
+            a.sc->csum = csum;
+        }
+    } else {
+        const float s2 = upper_total(a.tot_s, n, sh, chunk_tot, bcast);
+        if (threadIdx.x == 0) {
+            const float neff = __fdiv_rn(1.0f, s2);  // nEff = 1 / sum(w^2), core.cpp:788-791
+            a.sc->s2 = s2;
+            a.sc->neff = neff;
+            a.sc->did = (a.do_resample && neff < a.neff_threshold) ? 1 : 0;  // core.cpp:739
+        }
     }
 }
 
-// Step C: normalise (core.cpp:727-729 / 784-786: one quotient serves both), local CDF scan, totals of w and w^2.
-// pow(w,2) is a double product stored as float == one correctly rounded fp32 multiply.
-__global__ void __launch_bounds__(SLAM_SCAN_BLOCK) k_normalise_scan(float *__restrict__ w, size_t n,
-                                                                    const float *__restrict__ ws_ptr,
-                                                                    float *__restrict__ cdf_local,
-                                                                    float *__restrict__ tot_c,
-                                                                    float *__restrict__ tot_s) {
-    __shared__ float sh[32];
-    const size_t i = (size_t) blockIdx.x * SLAM_SCAN_BLOCK + threadIdx.x;
-    const float ws = *ws_ptr;
-    float wn = 0.0f;
-    if (i < n) {
-        wn = __fdiv_rn(w[i], ws);
-        w[i] = wn;
-    }
-    const float sq = __fmul_rn(wn, wn);
-    const float sc = block_scan_1024(wn, sh);
-    const float ss = block_scan_1024(sq, sh);
-    if (i < n) cdf_local[i] = sc;
-    const size_t last = min(n, ((size_t) blockIdx.x + 1) * SLAM_SCAN_BLOCK) - 1;
-    if (i == last) {
-        tot_c[blockIdx.x] = sc;
-        tot_s[blockIdx.x] = ss;
+// Grid-wide barrier of the cooperative launch, optionally with an exchange in the middle: every CTA arrives, CTA 0
+// waits for all arrivals, runs the exchange (peer stores + wait for the peers), then releases the grid.
+__device__ __forceinline__ unsigned gridbar_load(const unsigned *p) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void grid_barrier(const GridBar &g, int k, const XchgArgs *x) {
+    const unsigned G = gridDim.x;
+    const unsigned arrived = g.base + (unsigned) k * (G + 1u) + G, released = arrived + 1u;
+    __syncthreads();
+    if (blockIdx.x == 0) {
+        if (threadIdx.x == 0) {
+            __threadfence();
+            atomicAdd(g.ctr, 1u);
+            while ((int) (gridbar_load(g.ctr) - arrived) < 0) {
+            }
+            __threadfence();
+        }
+        __syncthreads();
+        if (x) xchg_body(*x);
+        if (threadIdx.x == 0) {
+            __threadfence();
+            atomicAdd(g.ctr, 1u);
+        }
+        __syncthreads();
+    } else {
+        if (threadIdx.x == 0) {
+            __threadfence();
+            atomicAdd(g.ctr, 1u);
+            while ((int) (gridbar_load(g.ctr) - released) < 0) {
+            }
+            __threadfence();
+        }
+        __syncthreads();
     }
 }
+#define SLAM_GRIDBAR_TICKS(G) (2u * ((G) + 1u))  // what one k_weights_fused launch adds to the counter
 
-// Step E: cdf = block_exclusive + local; in-block running maximum (mloc) and block maximum (bmax) so that the
-// search below runs on monotone keys even where the tree-ordered CDF dips by an ulp.
-// tot_c_scanned is indexed by GLOBAL block (block_offset = first global block of this device).
-__global__ void __launch_bounds__(SLAM_SCAN_BLOCK) k_cdf_finalise(float *__restrict__ cdf, size_t n,
-                                                                  const float *__restrict__ tot_c_scanned,
-                                                                  size_t block_offset, float *__restrict__ mloc,
-                                                                  float *__restrict__ bmax) {
+__global__ void __launch_bounds__(SLAM_SCAN_BLOCK, 1) k_weights_fused(const WeightsArgs a, const GridBar g,
+                                                                      const XchgArgs x1, const XchgArgs x2) {
     __shared__ float sh[32];
-    const size_t i = (size_t) blockIdx.x * SLAM_SCAN_BLOCK + threadIdx.x;
-    const size_t gb = block_offset + blockIdx.x;
-    float v = -INFINITY;
-    if (i < n) {
-        v = cdf[i];
-        if (gb > 0) v = __fadd_rn(tot_c_scanned[gb - 1], v);
-        cdf[i] = v;
-    }
-    const float mx = block_maxscan_1024(v, sh);
-    if (i < n) mloc[i] = mx;
-    const size_t last = min(n, ((size_t) blockIdx.x + 1) * SLAM_SCAN_BLOCK) - 1;
-    if (i == last) bmax[blockIdx.x] = mx;
+    __shared__ float chunk_tot[SLAM_SCAN_BLOCK];
+    __shared__ float bcast;
+    for (int lb = blockIdx.x; lb < a.nb; lb += gridDim.x) weights_phase_a(a, lb, sh);
+    grid_barrier(g, 0, x1.world > 1 ? &x1 : nullptr);
+    const float ws = upper_total(a.tot_w, a.nbg, sh, chunk_tot, &bcast);
+    for (int lb = blockIdx.x; lb < a.nb; lb += gridDim.x) weights_phase_c(a, lb, ws, sh);
+    grid_barrier(g, 1, x2.world > 1 ? &x2 : nullptr);
+    const int second = gridDim.x > 1 ? 1 : 0;
+    if (blockIdx.x == 0) weights_phase_d(a, 0, ws, sh, chunk_tot, &bcast);
+    if ((int) blockIdx.x == second) weights_phase_d(a, 1, ws, sh, chunk_tot, &bcast);
+}
+// The same pass as three launches (the exchanges are k_xchg launches in between).
+__global__ void __launch_bounds__(SLAM_SCAN_BLOCK) k_weights_a(const WeightsArgs a) {
+    __shared__ float sh[32];
+    weights_phase_a(a, blockIdx.x, sh);
+}
+__global__ void __launch_bounds__(SLAM_SCAN_BLOCK) k_weights_c(const WeightsArgs a) {
+    __shared__ float sh[32];
+    __shared__ float chunk_tot[SLAM_SCAN_BLOCK];
+    __shared__ float bcast;
+    const float ws = upper_total(a.tot_w, a.nbg, sh, chunk_tot, &bcast);
+    weights_phase_c(a, blockIdx.x, ws, sh);
+}
+__global__ void __launch_bounds__(SLAM_SCAN_BLOCK) k_weights_d(const WeightsArgs a) {
+    __shared__ float sh[32];
+    __shared__ float chunk_tot[SLAM_SCAN_BLOCK];
+    __shared__ float bcast;
+    const float ws = upper_total(a.tot_w, a.nbg, sh, chunk_tot, &bcast);
+    weights_phase_d(a, blockIdx.x, ws, sh, chunk_tot, &bcast);
 }
 
 // Step F: select[] (stratifiedRandom core.cpp:751-769; di precomputed by the reference's own fp32 accumulation
@@ -774,25 +897,38 @@ __global__ void __launch_bounds__(SLAM_SCAN_BLOCK) k_cdf_finalise(float *__restr
 // which case the host runs the exact sequential merge (k_keep_sequential).  keep = -1 where the reference leaves -1.
 struct SearchArgs {
     const float *di;       // [n_local] strata midpoints for this device's global slots
-    const double *unif;    // [n_local]
-    const float *cdf[SLAM_MAX_RANKS];   // [n_global]-indexed per rank; rank r = index / n_local holds that block.  When
-    const float *mloc[SLAM_MAX_RANKS];  // sharded these are the peers' buffers themselves (CUDA IPC over NVLink): a
-                                        // slot's search lands on its own rank unless the weights are badly skewed, so
-                                        // the two 4*Pg-byte all-gathers of the first version bought nothing
+    const double *unif;    // [n_local] (2-slot halo in front), or nullptr: the device generator (slam_rng.cuh)
+    unsigned long long seed;
+    unsigned draw;
+    const float *cdf[SLAM_MAX_RANKS];   // [n_global]-indexed per rank; rank r = index / n_local holds that block: the
+    const float *mloc[SLAM_MAX_RANKS];  // IN-BLOCK CDF and its running maximum (k_weights_*), to which the block prefix
+                                        // Tc[b-1] is added on the fly.  When sharded these are the peers' buffers
+                                        // themselves (CUDA IPC over NVLink): a slot's search lands on its own rank
+                                        // unless the weights are badly skewed
     int world;
+    const float *Tc;       // [nb_global] blocked scan of the block totals of the CDF
     const float *BM;       // [nb_global] prefix maxima of the block maxima
     float *sel;            // [n_local] out
     int *keep;             // [n_local] out (global indices)
     int *anomaly;          // out flag
+    int force_anomaly;     // test hook (SLAMGPU_FORCE_ANOMALY): report an unproven slot regardless
     size_t n_local, n_global, slot_offset;
     int nb_global;
     float k, khalf;        // 1/N and k/2 as the reference forms them
 };
 
-__device__ __forceinline__ float select_value(const SearchArgs &a, size_t c_local) {
+// c_local may be -1 / -2: the two slots before this device's first one (di and unif carry a 2-slot halo in front).
+__device__ __forceinline__ float select_value(const SearchArgs &a, long long c_local) {
     // *diter + unifRand()*k - k/2 evaluated in double, stored as float (core.cpp:767)
-    const double t = __dadd_rn((double) a.di[c_local], __dmul_rn(a.unif[c_local], (double) a.k));
+    const double u = a.unif ? a.unif[c_local]
+                            : rng_unif(a.seed, (unsigned long long) ((long long) a.slot_offset + c_local), a.draw);
+    const double t = __dadd_rn((double) a.di[c_local], __dmul_rn(u, (double) a.k));
     return __double2float_rn(__dsub_rn(t, (double) a.khalf));
+}
+// The final CDF / running maximum at global index i of block blk: block prefix + in-block value, one fp32 add exactly
+// as the blocked scan forms it (block 0 has no prefix).
+__device__ __forceinline__ float with_prefix(const SearchArgs &a, long long blk, float v) {
+    return blk > 0 ? __fadd_rn(a.Tc[blk - 1], v) : v;
 }
 
 __device__ __forceinline__ long long first_exceed(const SearchArgs &a, float s) {
@@ -810,7 +946,7 @@ __device__ __forceinline__ long long first_exceed(const SearchArgs &a, float s) 
     int l = 0, h = len - 1;  // the block's last running max exceeds s, so an answer exists
     while (l < h) {
         const int mid = (l + h) >> 1;
-        if (mloc[b0 + mid] > s) h = mid; else l = mid + 1;
+        if (with_prefix(a, lo, mloc[b0 + mid]) > s) h = mid; else l = mid + 1;
     }
     return (long long) (b0 + l);
 }
@@ -819,7 +955,7 @@ __device__ __forceinline__ long long first_exceed(const SearchArgs &a, float s) 
 // maximum of the CDF = max(prefix maximum of the earlier blocks, in-block running maximum).
 __device__ __forceinline__ float running_max_at(const SearchArgs &a, long long i) {
     const long long blk = i / SLAM_SCAN_BLOCK;
-    const float m = a.mloc[a.world > 1 ? (int) ((size_t) i / a.n_local) : 0][i];
+    const float m = with_prefix(a, blk, a.mloc[a.world > 1 ? (int) ((size_t) i / a.n_local) : 0][i]);
     return blk > 0 ? fmaxf(a.BM[blk - 1], m) : m;
 }
 
@@ -852,7 +988,7 @@ __device__ __forceinline__ long long warp_first_exceed(const SearchArgs &a, floa
     const size_t b0 = (size_t) blk * SLAM_SCAN_BLOCK;
     const int len = (int) min((size_t) SLAM_SCAN_BLOCK, a.n_global - b0);
     const float *mloc = a.mloc[a.world > 1 ? (int) (b0 / a.n_local) : 0] + b0;
-    return (long long) b0 + warp_first_true(0, len - 1, [&](int i) { return mloc[i] > s; });
+    return (long long) b0 + warp_first_true(0, len - 1, [&](int i) { return with_prefix(a, blk, mloc[i]) > s; });
 }
 
 // select[] is non-decreasing over a CTA's 256 slots, so every G of the CTA lies between the G of its first and of its
@@ -872,7 +1008,7 @@ __global__ void __launch_bounds__(256) k_search_keep(SearchArgs a) {
     float s = 0.0f;
     long long g = -1;
     if (c < a.n_local) {
-        s = select_value(a, c);
+        s = select_value(a, (long long) c);
         a.sel[c] = s;
     }
     const int n_here = (int) min((size_t) blockDim.x, a.n_local - c0);  // live slots of this CTA (>= 1)
@@ -887,12 +1023,11 @@ __global__ void __launch_bounds__(256) k_search_keep(SearchArgs a) {
             long long gh = -1;
             if (gc >= 0) {
                 const long long cl = (long long) c0 - 2 + wid;  // may be -1 / -2: halo stored before index 0
-                const double t = __dadd_rn((double) a.di[cl], __dmul_rn(a.unif[cl], (double) a.k));
-                gh = warp_first_exceed(a, __double2float_rn(__dsub_rn(t, (double) a.khalf)));
+                gh = warp_first_exceed(a, select_value(a, cl));
             }
             if ((threadIdx.x & 31) == 0) g_sh[wid] = gh;
         } else if (wid < 4) {
-            const float sw = select_value(a, wid == 2 ? c0 : c0 + n_here - 1);
+            const float sw = select_value(a, (long long) (wid == 2 ? c0 : c0 + n_here - 1));
             const long long gw = warp_first_exceed(a, sw);
             if ((threadIdx.x & 31) == 0) {
                 swin[wid - 2] = sw;
@@ -930,8 +1065,11 @@ __global__ void __launch_bounds__(256) k_search_keep(SearchArgs a) {
     const long long kprev = max(g1, g2);  // K[c-1]; -1 when c is global slot 0
     bool ok;
     if (g >= kprev) ok = true;
-    else ok = (kc == kprev) && (kprev == SENT || a.cdf[a.world > 1 ? (int) ((size_t) kprev / a.n_local) : 0][kprev] > s);
-    if (!ok) atomicExch(a.anomaly, 1);
+    else
+        ok = (kc == kprev) &&
+             (kprev == SENT || with_prefix(a, kprev / SLAM_SCAN_BLOCK,
+                                           a.cdf[a.world > 1 ? (int) ((size_t) kprev / a.n_local) : 0][kprev]) > s);
+    if (!ok || a.force_anomaly) atomicExch(a.anomaly, 1);
     a.keep[c] = (kc == SENT) ? -1 : (int) kc;
 }
 
@@ -949,6 +1087,50 @@ __global__ void k_keep_sequential(const float *__restrict__ sel, const float *__
             ctr++;
         }
     }
+}
+
+// The final CDF of this device's slots (block prefix + in-block value), for the sequential merge.
+__global__ void __launch_bounds__(256) k_cdf_final(const float *__restrict__ cdf_loc, const float *__restrict__ Tc,
+                                                   long long slot0, size_t n, float *__restrict__ out) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const long long blk = (slot0 + (long long) i) / SLAM_SCAN_BLOCK;
+    out[i] = blk > 0 ? __fadd_rn(Tc[blk - 1], cdf_loc[i]) : cdf_loc[i];
+}
+
+// The sequential merge, sharded: this rank's slots only, continuing from the CDF position the previous rank ended at
+// (slot c takes the first index >= the previous slot's index whose CDF exceeds select[c] — the same index may serve
+// again — exactly the while loop of core.cpp:802-806).  The CDF is read wherever it lives (rank = index / n_local).
+struct SeqArgs {
+    const float *cdf[SLAM_MAX_RANKS];  // [n_global]-indexed per rank, final values in the owner's block
+    const float *sel;                  // [n_local]
+    int *keep;                         // [n_local]
+    size_t n_local, n_global;
+    const long long *start;            // nullptr: from index 0
+    long long *end;
+};
+__global__ void k_keep_sequential_part(SeqArgs q) {
+    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    long long i = q.start ? *q.start : 0;
+    const long long n = (long long) q.n_global;
+    for (size_t c = 0; c < q.n_local; c++) {
+        const float s = q.sel[c];
+        while (i < n && !(s < q.cdf[(size_t) i / q.n_local][i])) i++;
+        q.keep[c] = (i < n) ? (int) i : -1;
+    }
+    *q.end = i;
+}
+
+// unifRand() from raw rand() values (slamgpu_update_i32): one IEEE double division, as core.cpp:776.
+__global__ void __launch_bounds__(256) k_ints_to_unif(const int *__restrict__ r, double *__restrict__ u, size_t n) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) u[i] = __ddiv_rn((double) r[i], (double) SLAM_RAND_MAX);
+}
+// Throughput mode in the one-thread reference order: the generator's uniforms written out.
+__global__ void __launch_bounds__(256) k_fill_unif(double *__restrict__ u, size_t n, unsigned long long seed,
+                                                   unsigned long long slot0, unsigned draw) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) u[i] = rng_unif(seed, slot0 + i, draw);
 }
 
 // REFERENCE order (SLAMGPU_SCAN_REFERENCE): one thread reproduces Eigen's SSE redux (Redux.h:193-248 with the SSE2
@@ -984,7 +1166,8 @@ __device__ float eigen_sum_seq(const float *v, long n) {
 
 __global__ void k_reference_weights(float *__restrict__ w, size_t n, const float *__restrict__ di,
                                     const double *__restrict__ unif, float k, float khalf, float *__restrict__ sq,
-                                    float *__restrict__ cdf, float *__restrict__ sel, float *__restrict__ neff_out) {
+                                    float *__restrict__ cdf, float *__restrict__ sel, Scalars *__restrict__ sc,
+                                    float neff_threshold, int do_resample) {
     if (blockIdx.x != 0 || threadIdx.x != 0) return;
     const float ws = eigen_sum_seq(w, (long) n);
     for (size_t i = 0; i < n; i++) {
@@ -993,7 +1176,11 @@ __global__ void k_reference_weights(float *__restrict__ w, size_t n, const float
         sq[i] = __fmul_rn(wn, wn);
     }
     const float s2 = eigen_sum_seq(sq, (long) n);
-    *neff_out = __fdiv_rn(1.0f, s2);
+    const float neff = __fdiv_rn(1.0f, s2);
+    sc->ws = ws;
+    sc->s2 = s2;
+    sc->neff = neff;
+    sc->did = (do_resample && neff < neff_threshold) ? 1 : 0;  // core.cpp:739
     float run = 0.0f;
     for (size_t i = 0; i < n; i++) {
         run = __fadd_rn(run, w[i]);
@@ -1022,7 +1209,10 @@ __global__ void __launch_bounds__(256) k_gather_pose(PeerMaps pm, int cur, float
                                                      float *__restrict__ w, const int *__restrict__ keep, size_t P,
                                                      long long n_global, float new_w, int rank,
                                                      unsigned long long *__restrict__ remote_sources,
-                                                     int *__restrict__ log_slot) {
+                                                     int *__restrict__ log_slot, const int *__restrict__ cond) {
+    // cond: the device-side resample decision (Scalars::did).  The kernel is launched BEFORE the host has read nEff back
+    // and does nothing when the decision went the other way, so the read-back overlaps it instead of preceding it.
+    if (cond && *cond == 0) return;
     const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     int remote = 0;
     if (p < P) {
@@ -1159,10 +1349,14 @@ __device__ __forceinline__ EstPartial est_block_reduce(EstPartial v) {
 }
 // One launch: every CTA reduces its particles to a partial; the CTA that finishes last (ticket counter) combines the
 // partials in index order — the same order whichever CTA that is — and resets the ticket for the next call.
-__global__ void __launch_bounds__(256) k_estimate(const float *__restrict__ xv, const float *__restrict__ w, size_t P,
+// pick_b: nullable device flag (Scalars::did); when set and nonzero the poses are read from xv_b (the buffer the
+// conditional pose gather has just filled) instead of xv_a.
+__global__ void __launch_bounds__(256) k_estimate(const float *__restrict__ xv_a, const float *__restrict__ xv_b,
+                                                  const int *__restrict__ pick_b, const float *__restrict__ w, size_t P,
                                                   long long offset, EstPartial *part, unsigned *ticket,
                                                   EstPartial *__restrict__ out) {
     __shared__ bool last;
+    const float *__restrict__ xv = (pick_b && *pick_b) ? xv_b : xv_a;
     EstPartial v;
     v.sx = 0; v.sy = 0; v.wmax = -INFINITY; v.imax = 0x7fffffffffffffffLL;
     for (size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x; p < P; p += (size_t) gridDim.x * blockDim.x) {

@@ -27,7 +27,7 @@ struct PeerMaps {  // this device's and (when sharded) the peers' buffers, index
     const float4 *cov[SLAM_MAX_RANKS];
     const float *cdf[SLAM_MAX_RANKS];   // each rank's [Pg]-indexed CDF / running-maximum buffers (its own block filled)
     const float *mloc[SLAM_MAX_RANKS];
-    float *slab[SLAM_MAX_RANKS];               // block-total arrays [4][nbg]: tot_w | tot_c | tot_s | bmax
+    float *slab[SLAM_MAX_RANKS];               // block-total arrays [5][nbg]: tot_w | tot_c | tot_s | lmax | bm
     unsigned long long *flags[SLAM_MAX_RANKS]; // [SLAM_MAX_RANKS] arrival counters of the peer-memory exchange
     double *unif[SLAM_MAX_RANKS];              // unif_base (2-slot halo in front)
     int world;
@@ -52,7 +52,12 @@ struct XchgArgs {
     const unsigned *blob_src;
     int blob_words, blob_off;
 };
-#define SLAM_XCHG_BLOB_WORDS 8  // sizeof(EstPartial) / 4
+#define SLAM_XCHG_BLOB_WORDS 12  // sizeof(TailBlob) / 4
+#define SLAM_XCHG_BLOB_SLOTS 3   // two landing areas alternate between consecutive tails, the third carries the
+                                 // sequential-merge chain of the keep[] fallback
+#define SLAM_SLAB_ARRAYS 5       // tot_w | tot_c | tot_s | lmax (exchanged) | bm (local)
+// word offset of the landing areas behind the arrays of a slab over nbg blocks (16-byte aligned: records hold doubles)
+#define SLAM_BLOB_BASE(nbg) ((SLAM_SLAB_ARRAYS * (size_t) (nbg) + 3) & ~(size_t) 3)
 
 struct PeerRows {  // landmark pools by rank, for kernels that read a particle's ancestor column wherever it lives
     const float2 *mean[SLAM_MAX_RANKS];
@@ -89,6 +94,31 @@ struct EstPartial {
     float wmax;
     float theta;  // filled by k_estimate's last CTA: heading of particle imax when it lives on this device
     long long imax;
+};
+
+// What the tail of a resample leaves for the host (and, sharded, pushes into every rank's slab): this device's part
+// of the pose estimate and whether its search met a slot it could not prove (k_search_keep).
+struct TailBlob {
+    EstPartial est;
+    int anomaly;
+    int pad[3];
+};
+
+// Device scalars of the resample with a pinned mirror on the host.
+struct Scalars {
+    float ws, s2, csum, neff;
+    int did;                            // the decision of core.cpp:739, taken on the device: do_resample && nEff < NEFFECTIVE
+    int comm_error;                     // sticky: a peer never arrived at an exchange (cleared only after it was reported)
+    unsigned long long remote_sources;  // resampled slots whose particle came from another device (running total)
+    int gauss_late;                     // sticky: a chunk of an in-flight noise upload never arrived (GaussArrival)
+    int pad[7];
+};
+
+// Grid-wide barrier of the cooperative weights kernel: a counter that only ever grows; `base` is its value before the
+// launch (the host knows it: every launch adds the same amount).
+struct GridBar {
+    unsigned *ctr;
+    unsigned base;
 };
 
 #define SLAM_GATHER_ROWS 4  // landmark rows moved per thread by the resample gather

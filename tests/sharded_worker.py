@@ -1,7 +1,8 @@
-"""Worker for tests/test_gpu_sharded.py (run under torchrun, one rank per GPU): the particle set is block-sharded over
-the ranks, every rank runs the same predict/update cycle through the C ABI, and rank 0 checks the gathered result
-against the ORACLE run on the whole set in one piece: keep[] bit-exact (global indices), weights and nEff bit-exact
-after normalisation, poses / landmarks within 1e-4, and the migrated particles a bit-exact copy of their sources."""
+"""Worker for tests/test_gpu_sharded.py (run under torchrun, one rank per GPU, world 2 / 4 / 8): the particle set is
+block-sharded over the ranks, every rank runs the same predict/update cycle through the C ABI, and rank 0 checks the
+gathered result against the ORACLE run on the whole set in one piece: keep[] bit-exact (global indices), weights and
+nEff bit-exact after normalisation, poses / landmarks within 1e-4, and the migrated particles a bit-exact copy of their
+sources.  Phases 2-4: fused re-columning across ranks, the device generator, and the sequential-merge chain."""
 import os
 import sys
 
@@ -133,7 +134,59 @@ def main():
             got = np.concatenate([p[k] for p in parts], axis=(0 if k == "w" else 1))
             assert np.array_equal(got, g1[k]), "phase 2 (fused, sharded) vs one device: " + k
         assert np.isfinite(g1["lm_mean"]).all()
+    # ---- phase 3: throughput mode.  The device generator is keyed by the GLOBAL particle index, so the sharded run and
+    # the one-device run draw the same noise: through slamgpu_update (no host noise at all) they stay bit-identical.
+    seed = 0xC0FFEE1234
+    f.seed(seed)
+    if f1:
+        f1.seed(seed)
+    for cycle in range(3):
+        for _ in range(2):
+            V, G, dt, phi = drive.controls()
+            f.predict(V, G, Q_DEFAULT, dt, phi)
+            if f1:
+                f1.predict(V, G, Q_DEFAULT, dt, phi)
+        zf, idf = drive.observe()
+        neff, did = f.update(zf, idf, np.zeros((0, 2), np.float32), d["R"])
+        keep = f.debug_read(2)
+        est = f.estimate()
+        if f1:
+            neff1, did1 = f1.update(zf, idf, np.zeros((0, 2), np.float32), d["R"])
+            assert (neff1, did1) == (neff, did) and np.array_equal(f1.debug_read(2)[sl], keep), "phase 3 cycle %d" % cycle
+            e1 = f1.estimate()
+            assert abs(est[0] - e1[0]) < 1e-9 and abs(est[1] - e1[1]) < 1e-9 and est[2] == e1[2], (est, e1)
+    g = f.download()
+    dist.all_gather_object(parts, g)
+    if rank == 0:
+        g1 = f1.download()
+        for k in ("xv", "Pv", "w", "lm_mean", "lm_cov"):
+            got = np.concatenate([p[k] for p in parts], axis=(0 if k == "w" else 1))
+            assert np.array_equal(got, g1[k]), "phase 3 (device generator, sharded) vs one device: " + k
         f1.close()
+    f.close()
+    # ---- phase 4: a search anomaly on any rank sends EVERY rank into the exact sequential merge, the ranks taking
+    # turns in rank order (capi.cu keep_fallback); forced here.  Result: the one-piece oracle's keep[], and the gather
+    # redone with it.
+    os.environ["SLAMGPU_FORCE_ANOMALY"] = "1"
+    f = slam_b200.FastSLAM(slam_b200.FASTSLAM2, Pl, Nf, wheel_base=WHEELBASE, sigma_phi=SIGMA_PHI,
+                           n_effective=Pg + 1, use_heading=True, scan_mode=slam_b200.SCAN_BLOCKED, device=local)
+    del os.environ["SLAMGPU_FORCE_ANOMALY"]
+    dist.broadcast(idbuf.zero_() if rank else idbuf.copy_(torch.frombuffer(
+        bytearray(slam_b200.FastSLAM.comm_unique_id()), dtype=torch.uint8)), 0)
+    f.comm_init(rank, world, idbuf.cpu().numpy().tobytes())
+    w4 = (np.random.default_rng(8).random(Pg) ** 6).astype(np.float32) + np.float32(1e-30)
+    u4 = np.random.default_rng(9).random(Pg)
+    f.upload(c(d["xv"][:, sl]), c(d["Pv"][:, sl]), c(w4[sl]), c(d["lm_mean"][:, sl]), c(d["lm_cov"][:, sl]), Nf)
+    keep, neff, did = f.resample(c(u4[sl]), want_keep=True)
+    assert did and f.stats()["keep_fallbacks"] == 1
+    g = f.download(landmarks=False)
+    dist.all_gather_object(parts, dict(g, keep=keep))
+    if rank == 0:
+        wn, keep_o, neff_o = o.resample_indices(w4, u4, scan_mode=1)
+        keep_all = np.concatenate([p["keep"] for p in parts])
+        assert neff == neff_o and np.array_equal(keep_all, keep_o), "phase 4: sequential-merge chain"
+        got = np.concatenate([p["xv"] for p in parts], axis=1)
+        assert np.array_equal(got, d["xv"][:, np.where(keep_o < 0, Pg - 1, keep_o)])
         print("SHARDED_OK world=%d" % world)
     f.close()
     dist.destroy_process_group()

@@ -1,10 +1,15 @@
-"""CPU, world_size 2 over gloo: the EXCHANGE PROTOCOL of the sharded resample reproduces the
-one-piece oracle bit for bit.  Each rank holds half of the weights and runs, in numpy, exactly the steps the CUDA
-library runs per device (slam_b200/csrc/capi.cu: resample_indices): per-1024-block scans locally, block totals
-all-gathered in rank order, the same upper-level scan on every rank, CDF all-gathered, select[] from local uniforms
-with a 2-slot halo from the previous rank, first-exceedance search on running maxima, keep = max(G[c], G[c-1]).
-The library moves the same data through peer memory (comm.cu k_xchg pushes the block totals and the halo, the search
-reads the peers' CDF in place); gloo all-gathers stand in for that here — what is checked is WHICH data every rank
+"""CPU, world_size 2 and 4 over gloo: the EXCHANGE PROTOCOL of the sharded resample reproduces
+the one-piece oracle bit for bit.  Each rank holds its block of the weights and runs, in numpy, exactly the steps the
+CUDA library runs per device (slam_b200/csrc/kernels.cuh k_weights_fused + k_search_keep, capi.cu resample_indices):
+  exchange 1: per-1024-block totals of w                      -> every rank: ws
+  exchange 2: block totals of the in-block CDF and of w^2, and the in-block MAXIMUM of the in-block CDF (+ the 2-slot
+              uniform halo)                                    -> every rank: Tc (scanned totals), nEff, BM
+  no third exchange: the final CDF is never formed.  Rounding is monotone, so the running maximum of the final CDF
+  inside block b is fl(Tc[b-1] + running max of the in-block CDF) and the block maximum is fl(Tc[b-1] + lmax[b]); the
+  search adds the prefix to the in-block values it probes in the owner's memory.
+  fallback: the exact sequential merge of core.cpp:800-806, the ranks taking turns in rank order.
+The library moves the data through peer memory (xchg.cuh pushes the block arrays and the halo, the search reads the
+peers' in-block arrays in place); gloo all-gathers stand in for that here — what is checked is WHICH data every rank
 must see at each step and that the result is the one-piece oracle's.  The device kernels themselves are checked on
 GPUs by tests/test_gpu_sharded.py."""
 import os
@@ -70,27 +75,36 @@ def worker(rank, world, port, P_local, q):
     w_all = (rng.random(Pg) ** 5).astype(f32)
     u_all = rng.random(Pg)
     sl = slice(rank * P_local, (rank + 1) * P_local)
-    w, u = w_all[sl], u_all[sl]
-    # A/B: totals of w -> ws
+    w = w_all[sl]
+    nbl = P_local // BLOCK
+    # A / exchange 1 / B: totals of w -> ws
     _, tot = block_scan(w)
     _, ws = upper_scan(allgather(tot))
-    # C/D: normalise, local cdf scan, totals of cdf and of w^2
+    # C: normalise, in-block CDF, its running maximum, totals
     wn = (w / ws).astype(f32)
     sq = (wn * wn).astype(f32)
     cdf_loc, tot_c = block_scan(wn)
     _, tot_s = block_scan(sq)
-    tc_scanned, _ = upper_scan(allgather(tot_c))
+    mloc_loc = np.maximum.accumulate(cdf_loc.reshape(nbl, BLOCK), axis=1).reshape(-1)
+    lmax = mloc_loc.reshape(nbl, BLOCK)[:, -1].copy()
+    # exchange 2 / D
+    tot_c_g, lmax_g = allgather(tot_c), allgather(lmax)
+    Tc, _ = upper_scan(tot_c_g)
     _, s2 = upper_scan(allgather(tot_s))
     neff = f32(1.0) / s2
-    # E: final cdf for the local blocks, all-gathered
-    b0 = rank * P_local // BLOCK
-    cdf = cdf_loc.copy()
-    for b in range(P_local // BLOCK):
-        gb = b0 + b
-        if gb > 0:
-            cdf[b * BLOCK:(b + 1) * BLOCK] = (tc_scanned[gb - 1] + cdf[b * BLOCK:(b + 1) * BLOCK]).astype(f32)
-    cdf_g = allgather(cdf)
-    M = np.maximum.accumulate(cdf_g)
+    nbg = Pg // BLOCK
+    prefix = np.concatenate([[f32(0)], Tc[:-1]]).astype(f32)
+    bmax = np.where(np.arange(nbg) > 0, (prefix + lmax_g).astype(f32), lmax_g)
+    BM = np.maximum.accumulate(bmax)
+    # what the search reads in the owners' memory: their in-block arrays (peer reads; an all-gather stands in)
+    cdf_loc_g, mloc_loc_g = allgather(cdf_loc), allgather(mloc_loc)
+    blk = np.arange(Pg) // BLOCK
+    key = np.where(blk > 0, (prefix[blk] + mloc_loc_g).astype(f32), mloc_loc_g)          # with_prefix(mloc)
+    M = np.where(blk > 0, np.maximum(BM[np.maximum(blk - 1, 0)], key), key)              # running_max_at
+    cdf_final = np.where(blk > 0, (prefix[blk] + cdf_loc_g).astype(f32), cdf_loc_g)
+    # the identities the kernel relies on
+    assert np.array_equal(M, np.maximum.accumulate(cdf_final))
+    assert np.array_equal(bmax, np.maximum.reduceat(cdf_final, np.arange(0, Pg, BLOCK)))
     # F: select for local slots (+2 halo from the previous rank), search, keep
     k = f32(1.0 / f32(Pg))
     di = np.zeros(Pg, f32)
@@ -107,14 +121,27 @@ def worker(rank, world, port, P_local, q):
     prev = np.concatenate([[-1] * (2 - halo), G])[1:1 + P_local] if halo < 2 else G[1:1 + P_local]
     keep = np.maximum(keep, prev)
     keep = np.where(keep >= Pg, -1, keep).astype(np.int32)
-    q.put((rank, keep, float(neff), wn))
+    # fallback chain (capi.cu keep_fallback / k_keep_sequential_part): rank r continues where rank r-1 ended
+    sel_own = sel[halo:]
+    keep_seq = np.full(P_local, -1, np.int32)
+    pos = torch.zeros(1, dtype=torch.int64)
+    for r in range(world):
+        if r == rank:
+            i = int(pos.item())
+            for c in range(P_local):
+                while i < Pg and not (sel_own[c] < cdf_final[i]):
+                    i += 1
+                keep_seq[c] = i if i < Pg else -1
+            pos[0] = i
+        dist.broadcast(pos, r)
+    q.put((rank, keep, float(neff), wn, keep_seq))
     dist.barrier()
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("P_local", [2048])
-def test_two_rank_protocol_equals_one_piece_oracle(oracle, P_local):
-    world, port = 2, 29611
+@pytest.mark.parametrize("world,P_local", [(2, 2048), (4, 1024)])
+def test_protocol_equals_one_piece_oracle(oracle, world, P_local):
+    port = 29611 + world
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     procs = [ctx.Process(target=worker, args=(r, world, port, P_local, q)) for r in range(world)]
@@ -134,3 +161,4 @@ def test_two_rank_protocol_equals_one_piece_oracle(oracle, P_local):
     assert np.array_equal(wn, wn_o)
     assert all(g[2] == float(neff_o) for g in got)
     assert np.array_equal(keep, keep_o)
+    assert np.array_equal(np.concatenate([g[4] for g in got]), keep_o)   # the sequential chain gives the same keep[]
