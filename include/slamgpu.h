@@ -176,6 +176,9 @@ int slamgpu_download_decimated(slamgpu_t *h, int64_t stride, float *xv_out, floa
 int slamgpu_download_slice(slamgpu_t *h, int64_t p0, int64_t n, float *xv, float *Pv, float *w, float *lm_mean,
                            float *lm_cov);
 
+/* Poses, pose covariances and weights of the listed particles (local indices), packed with P := n. */
+int slamgpu_download_poses_at(slamgpu_t *h, const int64_t *idx, int64_t n, float *xv, float *Pv, float *w);
+
 /* Parity instrumentation.  With capture on, every resample keeps a device copy of the weights as they entered it and
  * as they left the normalisation; slamgpu_debug_read copies an item of the LAST resample to the host ([P] each):
  * the weights before / after normalisation (float), keep[] (int32, global indices) and select[] (float).  The data

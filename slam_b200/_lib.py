@@ -15,7 +15,7 @@ EXPORTS = [
     "slamgpu_compute_jacobians", "slamgpu_compute_jacobians_batch", "slamgpu_estimate", "slamgpu_download_decimated",
     "slamgpu_timing_enable", "slamgpu_timing_read", "slamgpu_timing_reset", "slamgpu_launch_count", "slamgpu_stat",
     "slamgpu_comm_unique_id", "slamgpu_comm_init", "slamgpu_update_i32", "slamgpu_seed", "slamgpu_download_slice",
-    "slamgpu_debug_capture", "slamgpu_debug_read",
+    "slamgpu_debug_capture", "slamgpu_debug_read", "slamgpu_download_poses_at",
     "slamgpu_ekf_create", "slamgpu_ekf_destroy", "slamgpu_ekf_sim", "slamgpu_ekf_size", "slamgpu_ekf_set_state",
     "slamgpu_ekf_get_state", "slamgpu_ekf_get_pose", "slamgpu_ekf_launch_count",
 ]
@@ -82,6 +82,7 @@ def load():
                                      C.POINTER(C.c_float)]
     L.slamgpu_seed.argtypes = [vp, C.c_uint64, C.c_int32]
     L.slamgpu_download_slice.argtypes = [vp, C.c_int64, C.c_int64, fp, fp, fp, fp, fp]
+    L.slamgpu_download_poses_at.argtypes = [vp, ip, C.c_int64, fp, fp, fp]
     L.slamgpu_debug_capture.argtypes = [vp, C.c_int32]
     L.slamgpu_debug_read.argtypes = [vp, C.c_int32, vp]
     L.slamgpu_update_particles.argtypes = [vp, fp, ip, C.c_int32, fp, C.c_int32, fp, fp]

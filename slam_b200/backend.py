@@ -111,6 +111,14 @@ class FastSLAM:
         self._check(self._L.slamgpu_debug_read(self._h, int(which), out.ctypes.data))
         return out
 
+    def download_poses_at(self, idx):
+        idx = np.ascontiguousarray(idx, np.int64)
+        n = idx.size
+        out = dict(xv=np.empty((3, n), np.float32), Pv=np.empty((9, n), np.float32), w=np.empty(n, np.float32))
+        self._check(self._L.slamgpu_download_poses_at(self._h, idx.ctypes.data, n, _ptr(out["xv"]), _ptr(out["Pv"]),
+                                                      _ptr(out["w"])))
+        return out
+
     def download_slice(self, p0, n, landmarks=True):
         Nf = self.Nf
         out = dict(xv=np.empty((3, n), np.float32), Pv=np.empty((9, n), np.float32), w=np.empty(n, np.float32), Nf=Nf)

@@ -256,7 +256,12 @@ extern "C" int slamgpu_create(const slamgpu_config *cfg, slamgpu_t **out) {
     for (int l = 0; l < h->nf_cap; l++) h->phys[l] = l;
     for (int r = 0; r < h->spare; r++) h->free_rows.push_back(h->nf_cap + r);
     h->row_epoch.assign(h->nf_cap, 0);
-    h->H = cfg->log_epochs > 0 ? std::max(4, cfg->log_epochs) : 64;
+    h->H = cfg->log_epochs > 0 ? std::max(4, cfg->log_epochs) : 256;
+    {   // trickle batch: H / 32 resamples apart (1 for the short logs the tests use); SLAMGPU_TRICKLE_BATCH overrides
+        const char *e = getenv("SLAMGPU_TRICKLE_BATCH");
+        int B = e ? atoi(e) : h->H / 32;
+        h->trickle_batch = std::max(1, std::min(B, (h->H - 3) / 2));
+    }
     int r = create_impl(cfg, h);
     if (r != SLAMGPU_OK) {
         std::string keep = g_err;
@@ -1210,12 +1215,20 @@ static int resample_commit(slamgpu *h) {
         CU(cudaEventRecord(h->ev_log, h->log_stream));
         h->log_pending = true;
     }
-    // background trickle: the stalest rows, enough per resample that no row's backlog reaches the log length
-    const int per = (h->Nf + (h->H - 3)) / (h->H - 2);
+    // Background trickle: every row has to be re-columned before its backlog outgrows the log (H epochs).  The rows
+    // cost 48 B x P each, and bringing a row forward from epoch e costs one ancestor chain of (epoch - e) look-ups per
+    // particle — per GROUP of rows that share e, not per row.  So the trickle works in batches: every B-th resample
+    // it takes the stalest B x ceil(Nf / (H - 2 - B)) rows at once.  Rows that were re-columned by one batch share an
+    // epoch and come up together again ~H resamples later: ONE long chain serves the whole batch (with B = 1 every
+    // resample paid a chain of ~H steps for ~Nf / H rows).  No row waits longer than H - 2 epochs: all Nf rows pass
+    // in (H - 2 - B) / B batches, B resamples apart.
+    const int B = h->trickle_batch;
     std::vector<std::pair<long long, int>> order;
     for (int l = 0; l < h->Nf; l++)
         if (h->row_epoch[l] < h->epoch) order.push_back({h->row_epoch[l], l});
     std::sort(order.begin(), order.end());
+    const bool batch_now = (h->epoch % B) == 0;
+    const int per = batch_now ? (int) (((long long) h->Nf * B + (h->H - 3 - B)) / (h->H - 2 - B)) : 0;
     std::vector<int> pick;
     for (size_t i = 0; i < order.size(); i++)
         if ((int) i < per || h->epoch - order[i].first >= h->H - 1) pick.push_back(order[i].second);
@@ -1466,6 +1479,35 @@ extern "C" int slamgpu_estimate(slamgpu_t *h, double *x, double *y, double *t) {
     if (x) *x = h->est_x;
     if (y) *y = h->est_y;
     if (t) *t = h->est_t;
+    return SLAMGPU_OK;
+}
+
+extern "C" int slamgpu_download_poses_at(slamgpu_t *h, const int64_t *idx, int64_t n, float *xv, float *Pv, float *w) {
+    if (!h || !idx || n <= 0) return slam_fail(SLAMGPU_EINVAL, "bad argument");
+    for (int64_t j = 0; j < n; j++)
+        if (idx[j] < 0 || (size_t) idx[j] >= h->P) return slam_fail(SLAMGPU_EINVAL, "particle index outside [0, P)");
+    CU(cudaSetDevice(h->cfg.device));
+    RET(flush_predicts(h));
+    const size_t N = (size_t) n;
+    long long *d_idx = nullptr;
+    float *d_out = nullptr;
+    CU(cudaMalloc(&d_idx, sizeof(long long) * N));
+    cudaError_t e = cudaMalloc(&d_out, sizeof(float) * 13 * N);
+    std::vector<float> out(13 * N);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_idx, idx, sizeof(long long) * N, cudaMemcpyHostToDevice, h->stream);
+    if (e == cudaSuccess) {
+        k_pick_poses<<<grid_for(N, 256), 256, 0, h->stream>>>(h->soa(h->cur), h->P, d_idx, N, d_out);
+        h->launches++;
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out.data(), d_out, sizeof(float) * 13 * N, cudaMemcpyDeviceToHost, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    cudaFree(d_idx);
+    if (d_out) cudaFree(d_out);
+    if (e != cudaSuccess) return slam_fail(SLAMGPU_ECUDA, std::string("download_poses_at: ") + cudaGetErrorString(e));
+    if (xv) memcpy(xv, out.data(), sizeof(float) * 3 * N);
+    if (Pv) memcpy(Pv, out.data() + 3 * N, sizeof(float) * 9 * N);
+    if (w) memcpy(w, out.data() + 12 * N, sizeof(float) * N);
     return SLAMGPU_OK;
 }
 

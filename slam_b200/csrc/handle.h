@@ -60,6 +60,7 @@ struct slamgpu {
     std::vector<long long> row_epoch;
     long long epoch = 0;         // number of resamples applied to the poses so far
     int H = 0;                   // epochs of keep[] kept in the log
+    int trickle_batch = 1;       // resamples between two batches of the background trickle (capi.cu resample_commit)
     int *keeplog = nullptr;      // [H][Pg] global keep arrays, epoch e at slot e % H
     int *anc = nullptr;          // [P] scratch: composed ancestor map
     int *fb_list = nullptr, *fb_count = nullptr;  // [P], [1]: particles the fast FastSLAM2 kernel hands to the reference-order one

@@ -1406,6 +1406,18 @@ __global__ void __launch_bounds__(256) k_decimate(PoseSoA s, MapRing m, size_t P
         }
 }
 
+// Poses and weights of an arbitrary list of particles, packed ([3][n] | [9][n] | [n]): parity checks that follow
+// lineages through a 2^20-particle run read a few thousand poses per cycle without touching the landmark rows.
+__global__ void __launch_bounds__(256) k_pick_poses(PoseSoA s, size_t P, const long long *__restrict__ idx, size_t n,
+                                                    float *__restrict__ out) {
+    const size_t j = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const size_t p = (size_t) idx[j];
+    for (int c = 0; c < 3; c++) out[c * n + j] = s.xv[c * P + p];
+    for (int c = 0; c < 9; c++) out[(3 + c) * n + j] = s.Pv[c * P + p];
+    out[12 * n + j] = s.w[p];
+}
+
 // Synthetic-workload initialisation: replicate a tile of Pt particles over all P (dst[p] = tile[p % Pt]).
 __global__ void __launch_bounds__(256) k_tile_planes(const float *__restrict__ tile, size_t Pt, float *__restrict__ dst,
                                                      size_t P, int planes) {

@@ -74,9 +74,12 @@ SLAM_RNG_HD void rng_randn(const int *r, float *out) {
 #pragma unroll
     for (int k = 0; k < count; k++) {
         if ((k & 1) == 0) {
-            const float uk = (float) ((double) r[k] / (double) SLAM_RAND_MAX);
-            const float uk1 = (float) ((double) r[k + 1] / (double) SLAM_RAND_MAX);
-            float square = (float) (-2.0 * (double) logf(uk));
+            // rand() * 1.0 / RAND_MAX stored as float (core.cpp:392-394).  The double product with the reciprocal is the
+            // correctly rounded quotient except when that quotient sits within 2^-52 of a float rounding boundary
+            // (a handful of the 2^31 ints, one float ulp): a double multiply instead of a ~30-instruction division
+            const float uk = (float) ((double) r[k] * (1.0 / (double) SLAM_RAND_MAX));
+            const float uk1 = (float) ((double) r[k + 1] * (1.0 / (double) SLAM_RAND_MAX));
+            float square = -2.0f * logf(uk);  // exact doubling: the same float as the reference's double product
             if (square < 0.0f) square = 0.0f;
             amp = sqrtf(square);
             angle = (float) (2.0 * 3.14159265358979323846 * (double) uk1);

@@ -130,8 +130,10 @@ def test_resample_blocked_equals_sequential_on_exact_weights(sb, oracle):
 
 
 def _drive(sb, oracle, method, heading, noise, P, scan_mode, n_observe=8, max_obs=6, math_mode=0):
+    import replay
     from gpu_util import gpu_snapshot, make_backend
     from oracle.pyoracle import State
+    replay.CONTEXT = "drive method=%d heading=%d noise=%d P=%d math=%d" % (method, heading, noise, P, math_mode)
     cap = 40
     recs = make_records(oracle, 70 + method, method, P, n_observe=n_observe, use_heading=heading, predict_noise=noise,
                         max_obs=max_obs)
@@ -181,7 +183,9 @@ def test_drive_blocked_order_ragged_p(sb, oracle, method, math_mode):
 def test_one_step_against_reference_golden(sb, method, math_mode):
     """Each record applied to the REFERENCE's previous output state and compared with the reference's next output
     (tests/golden/drive_fs*_p100.npz, produced by the unmodified reference)."""
+    import replay
     from gpu_util import gpu_snapshot, make_backend, upload_snapshot
+    replay.CONTEXT = "golden one-step method=%d math=%d" % (method, math_mode)
     recs, outs, meta = load_golden(os.path.join(G, "drive_fs%d_p100.npz" % method))
     P, cap = int(meta["P"]), int(meta["nf_cap"])
     f = make_backend(method, P, cap, use_heading=True, n_effective=int(0.75 * P), scan_mode=sb.SCAN_REFERENCE,
