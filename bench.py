@@ -344,13 +344,25 @@ def measure(cx, a, L, slam_b200, P, Nf, K, steps, warmup, burn_in, full):
         state.update(resamples=0, steps=0)
         snap = dict(launches=f.launches, stats=f.stats())
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        trace = [] if os.environ.get("SLAM_BENCH_TRACE") else None
         cx.barrier()
         with torch.cuda.stream(stream):
             e0.record(stream)
             for i in range(steps):
-                one_step(i, mode)
+                neff, did, _ = one_step(i, mode)
+                if trace is not None:  # per-step device time and migration (diagnostics; perturbs the leg slightly)
+                    ev = torch.cuda.Event(enable_timing=True)
+                    ev.record(stream)
+                    trace.append((ev, did, f.stats()["remote_sources"], f.stats()["rows_moved"]))
             e1.record(stream)
         cx.barrier()
+        if trace:
+            prev, pr, pm, rows = e0, snap["stats"]["remote_sources"], snap["stats"]["rows_moved"], []
+            for ev, did, rs, mv in trace:
+                rows.append("%.3f%s r%.2f m%d" % (prev.elapsed_time(ev), "*" if did else " ", (rs - pr) / P, mv - pm))
+                prev, pr, pm = ev, rs, mv
+            print("[rank %d] %s leg, ms per step (* = resampled, r = remote fraction, m = rows re-columned): %s"
+                  % (rank, mode, " | ".join(rows)), file=sys.stderr, flush=True)
         ms = cx.max_over_ranks(e0.elapsed_time(e1)) / steps
         out = dict(ms_per_step=ms, value=Pg * K / (ms * 1e-3), launches=f.launches - snap["launches"],
                    resample_rate=state["resamples"] / max(1, state["steps"]))

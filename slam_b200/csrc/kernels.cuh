@@ -251,21 +251,28 @@ __device__ __forceinline__ void stage_obs_off(const ObsSet &o, int K, size_t P, 
 }
 #define SLAM_OBS_OFF_SMEM(K) ((sizeof(unsigned long long) + sizeof(float2)) * ((K) + 1))
 
-// Shared-memory staging of the FastSLAM2 fast kernels: source / destination element offsets (row * P) and z.
+// Shared-memory staging of the fast kernels: source / destination element offsets (row * P), z, and (sin, cos) of the
+// observed bearing (slam_math.cuh bearing_innovation: the pass over a fixed pose composes the ray's sine and cosine
+// from these and the pose's own instead of evaluating an arctangent per particle-landmark).
 template <bool REMAP>
 __device__ __forceinline__ void stage_obs_fs2(unsigned char *base, const ObsSet &o, int K, size_t P, float2 *&sz,
-                                              unsigned long long *&soff, unsigned long long *&doff) {
+                                              unsigned long long *&soff, unsigned long long *&doff, float2 *&ssc) {
     soff = reinterpret_cast<unsigned long long *>(base);
     doff = soff + K;
     sz = reinterpret_cast<float2 *>(doff + K);
+    ssc = sz + K;
     for (int i = threadIdx.x; i < K; i += blockDim.x) {
-        sz[i] = o.z[i];
+        const float2 z = o.z[i];
+        sz[i] = z;
+        float sb, cb;
+        sincosf(z.y, &sb, &cb);
+        ssc[i] = make_float2(sb, cb);
         soff[i] = (unsigned long long) o.row[i] * (unsigned long long) P;
         doff[i] = (unsigned long long) (REMAP ? o.row_dst[i] : o.row[i]) * (unsigned long long) P;
     }
     __syncthreads();
 }
-#define SLAM_OBS_FS2_SMEM(K) ((2 * sizeof(unsigned long long) + sizeof(float2)) * (K))
+#define SLAM_OBS_FS2_SMEM(K) ((2 * sizeof(unsigned long long) + 2 * sizeof(float2)) * (K))
 
 // anc: the resample's keep[] (or a composed ancestor map) for this device's slots; -1 means "the last particle"
 // exactly as in k_gather_pose (core.cpp:800-806 leaves -1 where select ran past the CDF).
@@ -299,9 +306,9 @@ __global__ void __launch_bounds__(128) k_fs2_update_listed(PoseSoA s, MapRing m,
                                                            const NoiseSrc noise,
                                                            const int *__restrict__ anc, PeerRows pr, long long n_global,
                                                            const int *__restrict__ list, const int *__restrict__ count) {
-    float2 *sz;
+    float2 *sz, *ssc;
     unsigned long long *soff, *doff;
-    stage_obs_fs2<REMAP>(slam_smem, o, K, P, sz, soff, doff);
+    stage_obs_fs2<REMAP>(slam_smem, o, K, P, sz, soff, doff, ssc);
     const int n = *count;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const size_t p = (size_t) list[i];
@@ -326,6 +333,15 @@ __device__ __forceinline__ void cp_async_8(void *smem_dst, const void *gsrc) {
 }
 __device__ __forceinline__ void cp_async_16(void *smem_dst, const void *gsrc) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned) __cvta_generic_to_shared(smem_dst)), "l"(gsrc)
+                 : "memory");
+}
+// 16 bytes through L1 as well.  Used for rows read at an ANCESTOR's column: after many resamples a whole shard descends
+// from a handful of columns, so thousands of warps ask for the same 32-byte sectors — on a peer device when the
+// ancestor migrated.  Through L1 those reads are served on the SM after the first one; with .cg every warp's copy went
+// over NVLink to the same address (measured at 2 GPUs: +2 ms on the update kernel of the rank whose ancestors had
+// moved, every time a long-unobserved row came back into view).
+__device__ __forceinline__ void cp_async_16_ca(void *smem_dst, const void *gsrc) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((unsigned) __cvta_generic_to_shared(smem_dst)), "l"(gsrc)
                  : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
@@ -385,9 +401,9 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS, 7) k_fs2_update_fast(Pose
     constexpr int D = SLAM_RING_DEPTH, T = SLAM_UPDATE_THREADS;
     float4 *const ring_cov = reinterpret_cast<float4 *>(slam_smem) + threadIdx.x;                // slot s at [s * T]
     float2 *const ring_mean = reinterpret_cast<float2 *>(reinterpret_cast<float4 *>(slam_smem) + D * T) + threadIdx.x;
-    float2 *sz;
+    float2 *sz, *ssc;
     unsigned long long *soff, *doff;
-    stage_obs_fs2<REMAP>(slam_smem + (sizeof(float4) + sizeof(float2)) * D * T, o, K, P, sz, soff, doff);
+    stage_obs_fs2<REMAP>(slam_smem + (sizeof(float4) + sizeof(float2)) * D * T, o, K, P, sz, soff, doff, ssc);
     const unsigned blk = REMAP ? spread_block(blockIdx.x, gridDim.x, pr.spread, SLAM_SPREAD_CHUNK_SLOTS / T) : blockIdx.x;
     const size_t p = (size_t) blk * blockDim.x + threadIdx.x;
     if (p >= P) return;
@@ -397,15 +413,21 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS, 7) k_fs2_update_fast(Pose
     const float2 *smean = mean_p;
     const float4 *scov = cov_p;
     if (REMAP) remap_source(pr, remap_column(anc, p, n_global), P, smean, scov);
-#define SLAM_SRC_MEAN(i) (((REMAP && soff[i] != doff[i]) ? smean : mean_p) + soff[i])
-#define SLAM_SRC_COV(i) (((REMAP && soff[i] != doff[i]) ? scov : cov_p) + soff[i])
+    // row i goes in flight into ring slot `slot`: its own column, or (stale) the ancestor's, then through L1 as well
+    auto fetch = [&](int i, int slot) {
+        const unsigned long long so = soff[i];
+        if (REMAP && so != doff[i]) {
+            cp_async_8(ring_mean + slot * T, smean + so);
+            cp_async_16_ca(ring_cov + slot * T, scov + so);
+        } else {
+            cp_async_8(ring_mean + slot * T, mean_p + so);
+            cp_async_16(ring_cov + slot * T, cov_p + so);
+        }
+    };
     // the first D-1 rows go in flight before anything else is looked at
 #pragma unroll
     for (int j = 0; j < D - 1; j++) {
-        if (j < K) {
-            cp_async_8(ring_mean + j * T, SLAM_SRC_MEAN(j));
-            cp_async_16(ring_cov + j * T, SLAM_SRC_COV(j));
-        }
+        if (j < K) fetch(j, j);
         cp_async_commit();
     }
     const float R[4] = {Rm.x, Rm.y, Rm.z, Rm.w};
@@ -428,10 +450,7 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS, 7) k_fs2_update_fast(Pose
             const int i = i0 + sl;
             if (i < K) {
                 const int j = i + D - 1;
-                if (j < K) {
-                    cp_async_8(ring_mean + ((sl + D - 1) % D) * T, SLAM_SRC_MEAN(j));
-                    cp_async_16(ring_cov + ((sl + D - 1) % D) * T, SLAM_SRC_COV(j));
-                }
+                if (j < K) fetch(j, (sl + D - 1) % D);
                 cp_async_commit();
                 cp_async_wait<D - 1>();  // one group per row: all but the newest D-1 have landed, row i among them
                 lm_load_at(ring_mean + sl * T, ring_cov + sl * T, xf, Pf);
@@ -444,6 +463,8 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS, 7) k_fs2_update_fast(Pose
     gauss_arrived_load(ga, noise, P, p, g3);
     float xs[3];
     const float ratio = proposal_finish_fast(x0, L0, x, pi, g3, xs);
+    float sth, cth;  // the sampled pose is fixed from here on: its sine and cosine once, not an arctangent per landmark
+    sincosf(xs[2], &sth, &cth);
 
     // pass 2: likelihood at the sampled pose + landmark EKF, written back in place.  The observations are independent
     // here, so they are walked BACKWARDS: the last D rows of pass 1 are still in the ring, and the rows read most
@@ -457,13 +478,10 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS, 7) k_fs2_update_fast(Pose
                 cp_async_wait<D - 1>();
                 lm_load_at(ring_mean + sl * T, ring_cov + sl * T, xf, Pf);
                 const unsigned long long off = doff[i];
-                if (i - D >= 0) {  // the slot just read takes row i - D
-                    cp_async_8(ring_mean + sl * T, SLAM_SRC_MEAN(i - D));
-                    cp_async_16(ring_cov + sl * T, SLAM_SRC_COV(i - D));
-                }
+                if (i - D >= 0) fetch(i - D, sl);  // the slot just read takes row i - D
                 cp_async_commit();
-                const float z[2] = {sz[i].x, sz[i].y};
-                like = like * likelihood_and_feature_update_fast(xs, R, xf, Pf, z);
+                const float2 sc = ssc[i];
+                like = like * likelihood_and_feature_update_fast(xs, sth, cth, R, xf, Pf, sz[i].x, sc.x, sc.y);
                 __stcs(m.mean + p + off, make_float2(xf[0], xf[1]));
                 __stcs(m.cov + p + off, make_float4(Pf[0], Pf[2], Pf[1], Pf[3]));
             }
@@ -472,8 +490,6 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS, 7) k_fs2_update_fast(Pose
     s.w[p] = s.w[p] * like * ratio;
     const float Z[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
     store_pose(s, P, p, xs, Z);
-#undef SLAM_SRC_MEAN
-#undef SLAM_SRC_COV
 }
 
 // REMAP as in k_fs2_update_fast: a stale observed row is read at the ancestor's column (on whichever rank holds it) and
@@ -481,15 +497,17 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS, 7) k_fs2_update_fast(Pose
 template <bool REMAP>
 __global__ void __launch_bounds__(256) k_fs1_update_fast(PoseSoA s, MapRing m, size_t P, ObsSet o, int K, float4 Rm,
                                                          const int *__restrict__ anc, PeerRows pr, long long n_global) {
-    float2 *sz;
+    float2 *sz, *ssc;
     unsigned long long *soff, *doff;
-    stage_obs_fs2<REMAP>(slam_smem, o, K, P, sz, soff, doff);
+    stage_obs_fs2<REMAP>(slam_smem, o, K, P, sz, soff, doff, ssc);
     const unsigned blk = REMAP ? spread_block(blockIdx.x, gridDim.x, pr.spread, SLAM_SPREAD_CHUNK_SLOTS / 256) : blockIdx.x;
     const size_t p = (size_t) blk * blockDim.x + threadIdx.x;
     if (p >= P) return;
     const float R[4] = {Rm.x, Rm.y, Rm.z, Rm.w};
     float x[3];
     load_pose(s, P, p, x, nullptr);
+    float sth, cth;
+    sincosf(x[2], &sth, &cth);
     float2 *const mean_p = m.mean + p;
     float4 *const cov_p = m.cov + p;
     const float2 *smean = mean_p;
@@ -509,8 +527,8 @@ __global__ void __launch_bounds__(256) k_fs1_update_fast(PoseSoA s, MapRing m, s
         const unsigned long long noff = soff[n];
         const bool stale = REMAP && noff != doff[n];
         lm_load_at((stale ? smean : mean_p) + noff, (stale ? scov : cov_p) + noff, nxf, nPf);
-        const float z[2] = {sz[i].x, sz[i].y};
-        wt = wt * likelihood_and_feature_update_fast(x, R, xf, Pf, z);
+        const float2 sc = ssc[i];
+        wt = wt * likelihood_and_feature_update_fast(x, sth, cth, R, xf, Pf, sz[i].x, sc.x, sc.y);
         const unsigned long long d = doff[i];
         __stcs(mean_p + d, make_float2(xf[0], xf[1]));
         __stcs(cov_p + d, make_float4(Pf[0], Pf[2], Pf[1], Pf[3]));

@@ -439,7 +439,9 @@ __device__ __forceinline__ float mufu_ex2(float x) {
 #define SLAM_RSQRT(x) mufu_rsqrt(x)
 #define SLAM_RCP(x) mufu_rcp(x)
 #define SLAM_EXP2(x) mufu_ex2(x)
+#define SLAM_SINCOS_APPROX(a, s, c) __sincosf((a), (s), (c))
 #else
+#define SLAM_SINCOS_APPROX(a, s, c) (*(s) = sinf(a), *(c) = cosf(a))
 #define SLAM_RSQRT(x) (1.0f / sqrtf(x))
 #define SLAM_RCP(x) (1.0f / (x))
 #define SLAM_EXP2(x) exp2f(x)
@@ -477,12 +479,35 @@ SLAM_HD float wrap_fast(float t) {
     return fmaf(k, SLAM_TWO_PI_LO, fmaf(-k, SLAM_TWO_PI_HI, t));
 }
 
-// computeJacobians (core.cpp:666-713) for one landmark: predicted range zp[0], UNWRAPPED predicted bearing zp[1] =
-// atan2(dy,dx) - theta (the caller wraps the innovation once), Hf, T = Hf * sym(Pf) (row-major; its transpose is the
-// PHt of choleskyUpdate) and the symmetrised innovation covariance S = Hf Pf Hf' + R as (s00, s10, s11).
+// The bearing innovation v1 = wrap(z_b - (atan2(dy, dx) - theta)) (core.cpp:686 + trigonometricOffset) WITHOUT an
+// arctangent per landmark.  With phi = z_b + theta (the observed ray in the world frame) and u = (dx, dy) / d the unit
+// vector to the landmark — which the Jacobian needs anyway — the innovation is the angle from u to the ray:
+//     sin v1 = sin(phi) ux - cos(phi) uy,    cos v1 = cos(phi) ux + sin(phi) uy.
+// An innovation is small when the filter works, so v1 = asin(sin v1) by its odd series up to s^9 (|s| <= 0.26, 15
+// degrees: truncation < 1e-8 rad); anything larger — and the far side, cos v1 <= 0, where the reference's wrap
+// matters — takes the arctangent, which returns the wrapped angle directly.  ~16 instructions instead of the ~29 of
+// atan2 + subtract + wrap, twice per particle-landmark.
+SLAM_HD float bearing_innovation(float sphi, float cphi, float ux, float uy) {
+    const float sn = fmaf(sphi, ux, -cphi * uy);
+    const float cs = fmaf(cphi, ux, sphi * uy);
+    if (fabsf(sn) <= 0.26f && cs > 0.0f) {
+        const float q = sn * sn;
+        float r = 0.030381944f;               // 105/3456
+        r = fmaf(r, q, 0.044642857f);         // 15/336
+        r = fmaf(r, q, 0.075f);               // 3/40
+        r = fmaf(r, q, 0.16666667f);          // 1/6
+        return fmaf(r * q, sn, sn);
+    }
+    return atan2_fast(sn, cs);
+}
+
+// computeJacobians (core.cpp:666-713) for one landmark: predicted range *dist, the unit vector to the landmark in
+// Hf[0..1] (first row of Hf), Hf, T = Hf * sym(Pf) (row-major; its transpose is the PHt of choleskyUpdate) and the
+// symmetrised innovation covariance S = Hf Pf Hf' + R as (s00, s10, s11).  The predicted bearing itself is never
+// formed: see bearing_innovation().
 // (S + S')/2 == Hf sym(Pf) Hf' + sym(R) exactly, so the stored Pf (row-major, off-diagonals possibly an ulp apart —
 // the reference never symmetrises P, core.cpp:290) enters through pm = (Pf01 + Pf10)/2 and S needs 3 entries, not 4.
-SLAM_HD void jacobian_fast(const float *xv, const float *R, const float *xf, const float *Pf, float *zp, float *Hf,
+SLAM_HD void jacobian_fast(const float *xv, const float *R, const float *xf, const float *Pf, float *dist, float *Hf,
                            float *T, float *S3) {
     const float dx = xf[0] - xv[0];
     const float dy = xf[1] - xv[1];
@@ -491,8 +516,7 @@ SLAM_HD void jacobian_fast(const float *xv, const float *R, const float *xf, con
     float d = d2 * rd;
     d = fmaf(0.5f * rd, fmaf(-d, d, d2), d);  // one Newton step: the range innovation cancels ~3 digits
     const float rd2 = rd * rd;
-    zp[0] = d;
-    zp[1] = atan2_fast(dy, dx) - xv[2];
+    *dist = d;
     Hf[0] = dx * rd;
     Hf[1] = dy * rd;
     Hf[2] = -dy * rd2;
@@ -637,9 +661,13 @@ struct ProposalInfo {
 // One observation of FastSLAM2::sampleProposal (fastslam2.cpp:314-350) in information form.
 SLAM_HD void proposal_step_fast(float *x, ProposalInfo &pi, const float *R, const float *xf, const float *Pf,
                                 const float *z) {
-    float zp[2], Hf[4], T[4], S[3];
-    jacobian_fast(x, R, xf, Pf, zp, Hf, T, S);
-    const float v0 = z[0] - zp[0], v1 = wrap_fast(z[1] - zp[1]);
+    float d, Hf[4], T[4], S[3];
+    jacobian_fast(x, R, xf, Pf, &d, Hf, T, S);
+    // the pose moves with every observation here, so sin / cos of the ray come from the special-function unit (abs.
+    // error ~5e-7: what reaches the proposal is that times the Kalman gain of one bearing on the pose, < 1e-8)
+    float sphi, cphi;
+    SLAM_SINCOS_APPROX(z[1] + x[2], &sphi, &cphi);
+    const float v0 = z[0] - d, v1 = bearing_innovation(sphi, cphi, Hf[0], Hf[1]);
     // G = S^-1 (symmetric): adjugate / det
     const float rdet = SLAM_RCP(fmaf(S[0], S[2], -S[1] * S[1]));
     const float g00 = S[2] * rdet, g01 = -S[1] * rdet, g11 = S[0] * rdet;
@@ -708,11 +736,14 @@ SLAM_HD float proposal_finish_fast(const float *x0, const float *L0, const float
 // Pass 2 for one observation at the (sampled) pose: likelihood factor (likelihoodGivenXv, fastslam2.cpp:370-400, or
 // FastSLAM1::computeWeight's term, fastslam1.cpp:91-118 — the same density) and the landmark EKF
 // (featureUpdate -> choleskyUpdate, core.cpp:132-175,275-291), sharing one factorisation of S.
-SLAM_HD float likelihood_and_feature_update_fast(const float *xs, const float *R, float *xf, float *Pf,
-                                                 const float *z) {
-    float zp[2], Hf[4], T[4], S[3];
-    jacobian_fast(xs, R, xf, Pf, zp, Hf, T, S);
-    const float v0 = z[0] - zp[0], v1 = wrap_fast(z[1] - zp[1]);
+// The pose is fixed over the K observations of this pass: its (sin, cos)(theta) are evaluated once per particle,
+// (sin, cos)(z_b) once per observation (staged with the observation set), and the ray's are their angle sum.
+SLAM_HD float likelihood_and_feature_update_fast(const float *xs, float sth, float cth, const float *R, float *xf,
+                                                 float *Pf, float z_range, float sz, float cz) {
+    float d, Hf[4], T[4], S[3];
+    jacobian_fast(xs, R, xf, Pf, &d, Hf, T, S);
+    const float sphi = fmaf(sz, cth, cz * sth), cphi = fmaf(cz, cth, -sz * sth);
+    const float v0 = z_range - d, v1 = bearing_innovation(sphi, cphi, Hf[0], Hf[1]);
     const float l00i = SLAM_RSQRT(S[0]);
     const float l10 = S[1] * l00i;
     const float l11i = SLAM_RSQRT(fmaf(-l10, l10, S[2]));
@@ -733,6 +764,11 @@ SLAM_HD float likelihood_and_feature_update_fast(const float *xs, const float *R
     Pf[2] -= c01;
     Pf[3] -= fmaf(w10, w10, w11 * w11);
     return like;
+}
+// The same with everything evaluated on the spot (one call per particle-landmark: tests, host emulation).
+SLAM_HD float likelihood_and_feature_update_fast(const float *xs, const float *R, float *xf, float *Pf,
+                                                 const float *z) {
+    return likelihood_and_feature_update_fast(xs, sinf(xs[2]), cosf(xs[2]), R, xf, Pf, z[0], sinf(z[1]), cosf(z[1]));
 }
 
 }  // namespace slam
