@@ -110,7 +110,7 @@ static void free_all(slamgpu *h) {
     void *dev[] = {h->pose[0], h->pose[1], h->w, h->lm_mean, h->lm_cov, h->gauss, h->unif_base, h->di_base, h->cdf,
                    h->mloc, h->sel, h->keep, h->tot_slab, h->xflags, h->d_sc, h->d_z,
                    h->d_rec_in, h->d_rec_out, h->d_est, h->keeplog, h->anc, h->d_phys, h->fb_list, h->fb_count,
-                   h->gauss_flags, h->est_ticket, h->gbar, h->d_tail, h->d_chain, h->dbg_w, h->unif_i};
+                   h->gauss_flags, h->est_ticket, h->gbar, h->d_tail, h->d_chain, h->dbg_w, h->unif_i, h->coarse};
     for (void *p : dev)
         if (p) cudaFree(p);
     if (h->h_sc) cudaFreeHost(h->h_sc);
@@ -159,6 +159,15 @@ static int setup_global(slamgpu *h) {
         h->keeplog = nullptr;
     }
     CU(cudaMalloc(&h->keeplog, sizeof(int) * (size_t) h->H * Pg));
+    // coarse maps: one per SLAM_COARSE_STRIDE epochs of the log (none for the short logs some tests use)
+    if (h->coarse) {
+        cudaFree(h->coarse);
+        h->coarse = nullptr;
+    }
+    h->coarse_stride = (h->H >= 4 * SLAM_COARSE_STRIDE && !getenv("SLAMGPU_NO_COARSE")) ? SLAM_COARSE_STRIDE : 0;
+    h->coarse_slots = h->coarse_stride ? h->H / h->coarse_stride : 0;
+    h->coarse_epoch.assign((size_t) h->coarse_slots, -1);
+    if (h->coarse_slots) CU(cudaMalloc(&h->coarse, sizeof(int) * (size_t) h->coarse_slots * Pg));
     // stratifiedRandom's deterministic midpoints, by the reference's own fp32 accumulation run exactly N times
     // (core.cpp:751-759; oracle so_stratified_di).  Only this device's slots (+2 halo) are kept.
     std::vector<float> di(h->P + 2, 0.0f);
@@ -442,6 +451,36 @@ static int peer_maps(slamgpu *h, PeerMaps *pm) {
     return SLAMGPU_OK;
 }
 
+// anc <- the ancestor map from epoch `from` back to epoch `to` (to < from <= h->epoch), continuing the map already in
+// anc (identity == false: anc then maps the current epoch to `from`) or starting at this device's own slots.
+// Hops: logged keep arrays, and the coarse maps across whole strides (kernels.cuh k_chain).
+static int launch_chain(slamgpu *h, int *anc, long long from, long long to, bool identity) {
+    const size_t Pg = h->Pg;
+    const int G = h->coarse_stride;
+    long long cur = from;
+    bool first = true;
+    while (cur > to) {
+        ChainHops hops;
+        hops.n = 0;
+        while (cur > to && hops.n < SLAM_CHAIN_HOPS) {
+            if (G > 0 && cur % G == 0 && cur - G >= to && h->coarse_epoch[(size_t) ((cur / G) % h->coarse_slots)] == cur) {
+                hops.map[hops.n++] = h->coarse + (size_t) ((cur / G) % h->coarse_slots) * Pg;
+                cur -= G;
+            } else {
+                hops.map[hops.n++] = h->keeplog + (size_t) (cur % h->H) * Pg;
+                cur -= 1;
+            }
+        }
+        k_chain<<<grid_for(h->P, 256), 256, 0, h->stream>>>(anc, h->P, (long long) h->slot0, (long long) Pg, hops,
+                                                            (identity && first) ? 1 : 0);
+        KCHECK();
+        LAUNCHED(h, SLAMGPU_T_GATHER);
+        h->stat_chain_steps += hops.n;
+        first = false;
+    }
+    return SLAMGPU_OK;
+}
+
 // Brings the listed logical rows up to the current resample epoch: column p <- column anc(p) of the stored row.
 // Rows are grouped by the epoch they belong to (newest first, so that one ancestor chain is extended group by group)
 // and moved in chunks into free physical rows; the vacated rows return to the pool.
@@ -471,11 +510,7 @@ static int materialise(slamgpu *h, const std::vector<int> &want) {
         if (identity && e == h->epoch - 1) {
             anc_ptr = h->keeplog + (size_t) (h->epoch % h->H) * Pg + h->slot0;  // one epoch back: keep[] itself
         } else {
-            k_chain<<<grid_for(P, 256), 256, 0, h->stream>>>(h->anc, P, (long long) h->slot0, (long long) Pg, h->keeplog,
-                                                            h->H, cur_e, e + 1, identity ? 1 : 0);
-            KCHECK();
-            LAUNCHED(h, SLAMGPU_T_GATHER);
-            h->stat_chain_steps += cur_e - e;
+            RET(launch_chain(h, h->anc, cur_e, e, identity));
             identity = false;
             cur_e = e;
             anc_ptr = h->anc;
@@ -754,12 +789,8 @@ static int plan_fused_remap(slamgpu *h, const int *idf, int K, std::vector<int> 
     } else {
         TimedSpan sp;
         RET(span_begin(h, SLAMGPU_T_GATHER, &sp));
-        k_chain<<<grid_for(h->P, 256), 256, 0, h->stream>>>(h->anc, h->P, (long long) h->slot0, (long long) h->Pg,
-                                                            h->keeplog, h->H, h->epoch, e + 1, 1);
-        KCHECK();
-        LAUNCHED(h, SLAMGPU_T_GATHER);
+        RET(launch_chain(h, h->anc, h->epoch, e, true));
         RET(span_end(h, &sp));
-        h->stat_chain_steps += h->epoch - e;
         *anc = h->anc;
     }
     for (int i = 0; i < K; i++) {
@@ -1199,8 +1230,22 @@ static int resample_commit(slamgpu *h) {
     h->stat_resamples++;
     h->cur ^= 1;
     int *slot = h->keeplog + (size_t) (h->epoch % h->H) * Pg;
+    if (h->world > 1) CU(cudaMemcpyAsync(slot + h->slot0, h->keep, sizeof(int) * P, cudaMemcpyDeviceToDevice, h->stream));
+    // a stride of the log has just been completed: compose it into one coarse map for this device's slots (the
+    // chain's first hop reads this device's part of the newest keep[], the others the whole earlier arrays)
+    int *coarse_new = nullptr;
+    if (h->coarse_stride && h->epoch % h->coarse_stride == 0 && h->epoch >= h->coarse_stride) {
+        const size_t cs = (size_t) ((h->epoch / h->coarse_stride) % h->coarse_slots);
+        coarse_new = h->coarse + cs * Pg;
+        h->coarse_epoch[cs] = -1;  // (the hops of this very chain must all be single keeps)
+        const int G = h->coarse_stride;
+        h->coarse_stride = 0;
+        int rc = launch_chain(h, coarse_new + h->slot0, h->epoch, h->epoch - G, true);
+        h->coarse_stride = G;
+        RET(rc);
+        h->coarse_epoch[cs] = h->epoch;
+    }
     if (h->world > 1) {
-        CU(cudaMemcpyAsync(slot + h->slot0, h->keep, sizeof(int) * P, cudaMemcpyDeviceToDevice, h->stream));
         // The peers' parts of this epoch's keep[] are only read by ancestor chains that START at a later epoch (a
         // chain's first step looks up its own slot, i.e. this device's part): the all-gather runs on its own stream
         // behind the coming predict / update and is waited for at the next resample.
@@ -1212,6 +1257,7 @@ static int resample_commit(slamgpu *h) {
         CU(cudaEventRecord(h->ev_keep, h->stream));
         CU(cudaStreamWaitEvent(h->log_stream, h->ev_keep, 0));
         RET(comm_allgather_i32(h->comm, slot, P, h->log_stream));
+        if (coarse_new) RET(comm_allgather_i32(h->comm, coarse_new, P, h->log_stream));
         CU(cudaEventRecord(h->ev_log, h->log_stream));
         h->log_pending = true;
     }

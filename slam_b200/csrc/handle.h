@@ -62,6 +62,9 @@ struct slamgpu {
     int H = 0;                   // epochs of keep[] kept in the log
     int trickle_batch = 1;       // resamples between two batches of the background trickle (capi.cu resample_commit)
     int *keeplog = nullptr;      // [H][Pg] global keep arrays, epoch e at slot e % H
+    int *coarse = nullptr;       // [coarse_slots][Pg] compositions of coarse_stride consecutive keep arrays (k_chain)
+    int coarse_stride = 0, coarse_slots = 0;
+    std::vector<long long> coarse_epoch;  // the epoch each coarse slot ends at (-1: empty)
     int *anc = nullptr;          // [P] scratch: composed ancestor map
     int *fb_list = nullptr, *fb_count = nullptr;  // [P], [1]: particles the fast FastSLAM2 kernel hands to the reference-order one
     slam::RowPair *d_pairs = nullptr, *h_pairs = nullptr;  // row-move lists (device / pinned), nf_cap entries

@@ -1269,17 +1269,25 @@ __global__ void __launch_bounds__(256) k_diag_ancestors(const int *__restrict__ 
     }
 }
 
-// anc[p] <- keep_{e_to}[ ... keep_{e_from}[ start ] ... ] for e = e_from down to e_to, where start = anc[p] (continuing
-// a chain) or this device's global slot (start_identity).  keeplog holds the last H global keep arrays, epoch e at
-// slot e % H, each n_global ints.
+// anc[p] <- map_{n-1}[ ... map_1[ map_0[ start ] ] ... ], start = anc[p] (continuing a chain) or this device's global
+// slot (start_identity).  A hop is one of the logged keep arrays (one resample back) or a COARSE map: the composition
+// of SLAM_COARSE_STRIDE consecutive keep arrays, built once when the epoch counter passes a multiple of the stride
+// (capi.cu resample_commit).  The host lists the hops, newest first (capi.cu plan_hops): single steps down to the next
+// multiple of the stride, coarse hops across the middle, single steps for the rest — at most 2 * (stride - 1) + H /
+// stride look-ups per particle for a row that fell H epochs behind, instead of H.  Every map holds n_global ints.
+#define SLAM_CHAIN_HOPS 64
+#define SLAM_COARSE_STRIDE 16
+struct ChainHops {
+    const int *map[SLAM_CHAIN_HOPS];
+    int n;
+};
 __global__ void __launch_bounds__(256) k_chain(int *__restrict__ anc, size_t P, long long slot0, long long n_global,
-                                               const int *__restrict__ keeplog, int H, long long e_from,
-                                               long long e_to, int start_identity) {
+                                               const ChainHops hops, int start_identity) {
     const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= P) return;
     long long a = start_identity ? slot0 + (long long) p : (long long) anc[p];
-    for (long long e = e_from; e >= e_to; e--) {
-        long long k = keeplog[(size_t) (e % H) * (size_t) n_global + (size_t) a];
+    for (int h = 0; h < hops.n; h++) {
+        const long long k = hops.map[h][a];
         a = (k < 0) ? n_global - 1 : k;
     }
     anc[p] = (int) a;
