@@ -1025,6 +1025,14 @@ static int resample_indices(slamgpu *h, const UnifChoice &uc) {
     wa.do_resample = h->cfg.do_resample;
     const int arr1[1] = {0}, arr2[3] = {1, 2, 3};
     const bool halo = !uc.rng;  // the generator can produce any slot's uniform anywhere: nothing to send
+    if (h->world > 1 && h->log_pending) {
+        // The all-gather of the previous keep[] (NCCL, own stream) has had a whole update kernel to finish; it must not
+        // still be running next to the cooperative launch below.  A cooperative grid starts only when every CTA fits,
+        // an NCCL kernel holding SM resources can delay that — and if this rank's NCCL kernel waits for a peer whose
+        // SMs are full of a weights kernel spinning in its exchange for THIS rank's weights kernel, nobody moves.
+        CU(cudaStreamWaitEvent(h->stream, h->ev_log, 0));
+        h->log_pending = false;
+    }
     if (h->coop_grid > 0) {
         // ONE launch: both grid-wide barriers and (sharded) both exchanges happen inside the kernel
         XchgArgs x1, x2;

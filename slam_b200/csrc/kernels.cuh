@@ -1385,7 +1385,28 @@ __global__ void __launch_bounds__(256) k_estimate(const float *__restrict__ xv_a
     const float *__restrict__ xv = (pick_b && *pick_b) ? xv_b : xv_a;
     EstPartial v;
     v.sx = 0; v.sy = 0; v.wmax = -INFINITY; v.imax = 0x7fffffffffffffffLL;
-    for (size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x; p < P; p += (size_t) gridDim.x * blockDim.x) {
+    const size_t gtid = (size_t) blockIdx.x * blockDim.x + threadIdx.x, gstride = (size_t) gridDim.x * blockDim.x;
+    size_t done = 0;
+    if ((P & 3) == 0 && (reinterpret_cast<uintptr_t>(xv) & 15) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0) {
+        // four particles per thread and trip, the three 16-byte loads independent of each other
+        const float4 *x4 = reinterpret_cast<const float4 *>(xv), *y4 = reinterpret_cast<const float4 *>(xv + P),
+                     *w4 = reinterpret_cast<const float4 *>(w);
+        for (size_t q = gtid; q < P / 4; q += gstride) {
+            const float4 a = x4[q], b = y4[q], c = w4[q];
+            const float xs[4] = {a.x, a.y, a.z, a.w}, ys[4] = {b.x, b.y, b.z, b.w}, ws[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                v.sx += xs[j];
+                v.sy += ys[j];
+                if (ws[j] > v.wmax) {  // within a thread indices only grow: the first maximum wins by itself
+                    v.wmax = ws[j];
+                    v.imax = offset + (long long) (4 * q + j);
+                }
+            }
+        }
+        done = P;
+    }
+    for (size_t p = done + gtid; p < P; p += gstride) {
         EstPartial o;
         o.sx = xv[p];
         o.sy = xv[P + p];

@@ -589,13 +589,11 @@ struct PredictTick {
 };
 
 SLAM_HD void predict_tick_fast(float *x, float *C, const PredictTick &t, bool with_cov, bool use_heading) {
+    // sin / cos of the heading from the special-function unit (abs. error ~5e-7): they only enter multiplied by
+    // V*dt (centimetres per tick), i.e. ~4e-8 m per tick on the pose and as much, relatively, on the covariance
+    // increments — and the accurate sincosf was a quarter of this kernel's instructions (it is fp32-issue bound)
     float s, c;
-#if defined(__CUDA_ARCH__)
-    sincosf(t.G + x[2], &s, &c);
-#else
-    s = sinf(t.G + x[2]);
-    c = cosf(t.G + x[2]);
-#endif
+    SLAM_SINCOS_APPROX(wrap_fast(t.G + x[2]), &s, &c);
     const float a = -t.vdt * s, b = t.vdt * c;
     if (with_cov) {
         // T1 = Gv*C: rows 0 and 1 pick up a, b times row 2;  T2 = T1*Gv': columns 0 and 1 pick up a, b times column 2

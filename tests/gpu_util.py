@@ -27,3 +27,14 @@ def gpu_snapshot(f):
         d["lm_mean"] = np.zeros((0, f.P, 2), np.float32)
         d["lm_cov"] = np.zeros((0, f.P, 4), np.float32)
     return d
+
+
+def followed_iterations(a, g, tol=1e-4):
+    """Rows over which trace `a` stays within tol of trace `g` (columns 4:6 estimate x, y relative to max(1, |xy|), column
+    6 heading, absolute, modulo 2 pi), counted from the first row up to the first violation."""
+    scale = np.maximum(1.0, np.abs(g[:, 4:6]).max(axis=1))
+    err = np.maximum(np.abs(a[:, 4:6] - g[:, 4:6]).max(axis=1) / scale,
+                     np.abs((a[:, 6] - g[:, 6] + np.pi) % (2 * np.pi) - np.pi))
+    bad = np.nonzero(~(err <= tol))[0]
+    n = int(bad[0]) if bad.size else len(err)
+    return n, (float(err[:n].max()) if n else 0.0)

@@ -146,10 +146,14 @@ def main():
             f.predict(V, G, Q_DEFAULT, dt, phi)
             if f1:
                 f1.predict(V, G, Q_DEFAULT, dt, phi)
+        ep = f.estimate()  # after predict ticks: computed on request (a launch + one exchange of the rank partials)
+        if f1:
+            e1 = f1.estimate()
+            assert abs(ep[0] - e1[0]) < 1e-9 and abs(ep[1] - e1[1]) < 1e-9 and ep[2] == e1[2], (ep, e1)
         zf, idf = drive.observe()
         neff, did = f.update(zf, idf, np.zeros((0, 2), np.float32), d["R"])
         keep = f.debug_read(2)
-        est = f.estimate()
+        est = f.estimate()  # after an update: the value the resample's tail already produced
         if f1:
             neff1, did1 = f1.update(zf, idf, np.zeros((0, 2), np.float32), d["R"])
             assert (neff1, did1) == (neff, did) and np.array_equal(f1.debug_read(2)[sl], keep), "phase 3 cycle %d" % cycle

