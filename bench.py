@@ -76,7 +76,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -386,12 +386,17 @@ def measure(cx, a, L, slam_b200, P, Nf, K, steps, warmup, burn_in, full):
 
     res = {"P": P, "Nf": Nf, "K": K, "Pg": Pg, "npool": NPOOL}
     f.seed(20261104)                       # throughput mode: the device draws what the reference draws inside update()
-    res["cold"] = device_leg("rng", False)
-    for i in range(burn_in):
-        one_step(i, "rng")
+    # The clock sampler (nvidia-smi, polling) is started well BEFORE the timed legs and left running through them:
+    # its start-up initialises NVML on every GPU of the node, which stalls running CUDA work for milliseconds (measured:
+    # +0.9 ms per step over a 20-step leg at 8 GPUs when it was started right in front of the leg).
     clocks = ClockSampler(cx.local)
     if rank == 0:
         clocks.start()
+        time.sleep(1.5)
+    cx.barrier()
+    res["cold"] = device_leg("rng", False)
+    for i in range(burn_in):
+        one_step(i, "rng")
     res["value"] = device_leg("rng", False)
     res["profiled"] = device_leg("rng", True)
     res["clocks"] = clocks.stop() if rank == 0 else None
