@@ -266,6 +266,7 @@ def measure(cx, a, L, slam_b200, P, Nf, K, steps, warmup, burn_in, full):
        cold     throughput mode from the balanced initial population (what a 20-step run from scratch sees)
        [burn_in untimed steps: lineages coalesce, shards drift apart, the re-column backlog builds up]
        value    throughput mode, steady state, CUDA events on the library's stream          -> the headline
+       long     the value leg again over max(200, 10 K) steps (low-variance steady state)   -> `steady_long`
        profiled the same again with one CUDA-event pair around every kernel family (the events cost host time between
                 the launches, which is why the headline leg runs without them)            -> the roofline
        staged   one host-drawn noise set staged in HBM and reused (round 1's `value` leg, for continuity)
@@ -306,7 +307,7 @@ def measure(cx, a, L, slam_b200, P, Nf, K, steps, warmup, burn_in, full):
     # measured as GPU idle time), and each step's zf / idf sit in their own pinned slots.
     drive = SyntheticDrive(d["lm"], K, d["R"], seed=12345)  # same observations on every rank
     n_legs = 7 if full else 3
-    n_plan = n_legs * (warmup + steps) + burn_in + 4
+    n_plan = n_legs * (warmup + steps) + burn_in + 4 + (warmup + max(200, 10 * steps) if full else 0)
     zall, zall_p = pin((n_plan, K, 2), np.float32)
     iall, iall_p = pin((n_plan, K), np.int32)
     plan = []
@@ -335,7 +336,7 @@ def measure(cx, a, L, slam_b200, P, Nf, K, steps, warmup, burn_in, full):
         state["steps"] += 1
         return neff, did, est
 
-    def device_leg(mode, timing):
+    def device_leg(mode, timing, steps=steps):
         for i in range(warmup):
             one_step(i, mode)
         if timing:
@@ -399,6 +400,10 @@ def measure(cx, a, L, slam_b200, P, Nf, K, steps, warmup, burn_in, full):
         one_step(i, "rng")
     res["value"] = device_leg("rng", False)
     res["profiled"] = device_leg("rng", True)
+    if full:
+        # Migration between shards comes in bursts (a shard of sibling particles loses or gains weight as a whole), so
+        # K = 20 steps are a noisy sample of the steady state at N > 1: the same leg over 10 K (>= 200) steps, beside it
+        res["long"] = device_leg("rng", False, steps=max(200, 10 * steps))
     res["clocks"] = clocks.stop() if rank == 0 else None
     v = res["profiled"]
     remote = v["stats"]["remote_sources"] / max(1, v["stats"]["resamples"] * P)
@@ -630,6 +635,11 @@ def run_ours(a):
                 "dtype": "f32", "data": "synthetic",
                 "value_cold": res["cold"]["value"], "ms_per_step_cold": res["cold"]["ms_per_step"],
                 "value_staged_noise": res["staged"]["value"], "ms_per_step_staged_noise": res["staged"]["ms_per_step"],
+                "steady_long": {"steps": max(200, 10 * a.steps), "value": res["long"]["value"],
+                                "ms_per_step": res["long"]["ms_per_step"],
+                                "resample_rate": res["long"]["resample_rate"],
+                                "remote_fraction_rank0": res["long"]["stats"]["remote_sources"]
+                                / max(1, res["long"]["stats"]["resamples"] * P)},
                 "config": {"workload": "FastSLAM2 synthetic: %d particles/GPU x %d landmarks x %d observations/step, "
                                        "8 predict ticks per update (BASELINE.json config 4 shape)" % (P, Nf, K),
                            "particles_total": res["Pg"], "parallelism": "particles block-sharded over %d GPU(s)" % world,

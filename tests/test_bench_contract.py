@@ -59,7 +59,10 @@ def test_committed_cuda_line_carries_the_contract():
     assert d["gpu_launches"] > 0
     e = d["e2e"]
     assert e["unit"] == d["unit"] and e["h2d_bytes_per_step"] > 16e6 and e["d2h_bytes_per_step"] > 0
-    assert 0 < e["value"] <= d["value"] * 1.05  # host noise goes up every step: the end-to-end leg cannot be far ahead
+    # host noise goes up every step: the end-to-end leg cannot be ahead of the device-resident legs (each leg times its
+    # own K steps of the run, and K = 20 steps differ by how many of them resample)
+    best = max(d["value"], d["value_cold"], d["value_staged_noise"], d.get("steady_long", {}).get("value", 0))
+    assert 0 < e["value"] <= best * 1.05
     assert d["e2e_device_rng"]["h2d_bytes_per_step"] < 4096
     rf = d["roofline"]
     assert rf["bound"] == "hbm" and rf["unit"] == "GB/s" and abs(rf["frac"] - rf["achieved"] / rf["peak"]) < 1e-9
