@@ -77,7 +77,7 @@ static int flush_predicts(slamgpu *h);
 
 // ---- library-level -------------------------------------------------------------------------------------
 extern "C" const char *slamgpu_last_error(void) { return g_err.c_str(); }
-extern "C" const char *slamgpu_version(void) { return "slamgpu 0.1 sm_100a"; }
+extern "C" const char *slamgpu_version(void) { return "slamgpu 0.2 sm_100a"; }
 
 extern "C" void *slamgpu_host_alloc(uint64_t bytes) {
     void *p = nullptr;

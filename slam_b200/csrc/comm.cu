@@ -1,14 +1,16 @@
 // comm.cu — exchange steps of the sharded resample, one process per device.
 //
-//   * the small exchanges of the resample (per-1024-block weight totals, CDF totals, block maxima, the 2-slot uniform
-//     halo) and the stream-ordered barriers are ONE tiny kernel each over peer memory (k_xchg below): every rank
-//     stores its chunk into every peer's copy and waits on arrival counters; the CDF itself is never moved, the
-//     search reads it through the peer mappings;
+//   * the small exchanges of the resample (per-1024-block weight totals; CDF totals, w^2 totals and in-block maxima;
+//     the 2-slot uniform halo; the tail record) go over peer memory: every rank stores its chunk into every peer's
+//     copy and waits on arrival counters (xchg.cuh).  The two exchanges of the weights pass run INSIDE the cooperative
+//     weights kernel (kernels.cuh k_weights_fused, CTA 0 between the arrival and the release of a grid-wide barrier);
+//     the tail record and the occasional barrier are the stand-alone 1-CTA kernel k_xchg below.  The CDF itself is
+//     never moved, the search reads it through the peer mappings;
 //   * particle migration is NOT a collective: every rank maps its peers' pose and landmark buffers (CUDA IPC over
 //     NVLink / NVSwitch) and the gather / update kernels (kernels.cuh K7, K3 REMAP) read particles[keep[i]] straight
-//     from the owning device, with a barrier between batches because freed physical rows are recycled;
-//   * NCCL remains for the bootstrap (the IPC handles travel in one all-gather) and the all-gather of keep[] into the
-//     log (its own stream, off the critical path).  It is loaded at run time
+//     from the owning device, with a barrier only where the row tags of capi.cu order_rows ask for one;
+//   * NCCL remains for the bootstrap (the IPC handles travel in one all-gather) and the all-gather of keep[] and of the
+//     coarse ancestor maps into the log (its own stream, off the critical path).  It is loaded at run time
 //     from libnccl.so.2 (the copy torch already mapped when the caller is a torchrun rank, else the system one) so
 //     that a single-device build has no NCCL dependency.
 #include <dlfcn.h>
