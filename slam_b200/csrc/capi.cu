@@ -751,6 +751,7 @@ static int stage_obs_host(slamgpu *h, const float *z, const int *rows, const int
 // steady state: the rows observed last step were brought up to date then) the FastSLAM2 update kernel itself reads
 // them through the ancestor map and writes the updated landmarks into fresh physical rows.  Fills src / dst physical
 // rows per observation; *anc == nullptr means "nothing to fuse" (rows are current, or the general path ran).
+#define SLAM_REMAP_MIN_ROWS 3
 static int plan_fused_remap(slamgpu *h, const int *idf, int K, std::vector<int> &src, std::vector<int> &dst,
                             const int **anc, std::vector<int> &vacated) {
     *anc = nullptr;
@@ -773,7 +774,11 @@ static int plan_fused_remap(slamgpu *h, const int *idf, int K, std::vector<int> 
             i = j;
         }
         std::vector<int> others;
-        const bool fuse = (int) h->free_rows.size() >= n_stale;
+        // Fusing pays when many observed rows are stale (right after a resample: all K of them).  For a newcomer or two
+        // (a landmark coming into view on a step that follows no resample) the REMAP instantiation of the update kernel
+        // would cost more than it saves: it carries ~25 more instructions per particle-landmark for ALL K rows (~30 us at
+        // cfg 4), a separate re-column pass ~12 us per row.
+        const bool fuse = (int) h->free_rows.size() >= n_stale && n_stale >= SLAM_REMAP_MIN_ROWS;
         for (int i = 0; i < K; i++) {
             const long long re = h->row_epoch[idf[i]];
             if (re < h->epoch && (!fuse || re != e)) others.push_back(idf[i]);

@@ -483,19 +483,21 @@ SLAM_HD float wrap_fast(float t) {
 // arctangent per landmark.  With phi = z_b + theta (the observed ray in the world frame) and u = (dx, dy) / d the unit
 // vector to the landmark — which the Jacobian needs anyway — the innovation is the angle from u to the ray:
 //     sin v1 = sin(phi) ux - cos(phi) uy,    cos v1 = cos(phi) ux + sin(phi) uy.
-// An innovation is small when the filter works, so v1 = asin(sin v1) by its odd series up to s^9 (|s| <= 0.26, 15
-// degrees: truncation < 1e-8 rad); anything larger — and the far side, cos v1 <= 0, where the reference's wrap
-// matters — takes the arctangent, which returns the wrapped angle directly.  ~16 instructions instead of the ~29 of
-// atan2 + subtract + wrap, twice per particle-landmark.
+// An innovation is small when the filter works, so v1 = asin(sin v1) by an odd polynomial for |sin v1| <= 0.5 (30
+// degrees: max error 6e-8 rad; wide enough that a warp almost never has a lane outside it, which would make the whole
+// warp execute both branches); anything larger — and the far side, cos v1 <= 0, where the reference's wrap matters —
+// takes the arctangent, which returns the wrapped angle directly.  ~16 instructions instead of the ~29 of atan2 +
+// subtract + wrap, twice per particle-landmark.
 SLAM_HD float bearing_innovation(float sphi, float cphi, float ux, float uy) {
     const float sn = fmaf(sphi, ux, -cphi * uy);
     const float cs = fmaf(cphi, ux, sphi * uy);
-    if (fabsf(sn) <= 0.26f && cs > 0.0f) {
+    if (fabsf(sn) <= 0.5f && cs > 0.0f) {
+        // asin(s) = s + s^3 g(s^2), g a cubic fitted (minimax) on s^2 in [0, 0.25]: max |error| 6e-8 rad in fp32
         const float q = sn * sn;
-        float r = 0.030381944f;               // 105/3456
-        r = fmaf(r, q, 0.044642857f);         // 15/336
-        r = fmaf(r, q, 0.075f);               // 3/40
-        r = fmaf(r, q, 0.16666667f);          // 1/6
+        float r = 0.05159852f;
+        r = fmaf(r, q, 0.03918817f);
+        r = fmaf(r, q, 0.07554101f);
+        r = fmaf(r, q, 0.16664924f);
         return fmaf(r * q, sn, sn);
     }
     return atan2_fast(sn, cs);
