@@ -146,9 +146,32 @@ RunResult run_fastslam(int method, const Conf &conf, const Map &map, PlotSink *p
             }
             for (int64_t p = 0; p < P; p++) unif[p] = unif_rand();  // stratifiedRandom, on every update
             int32_t did = 0;
+            float neff = 0;
             rc = slamgpu_update(h, K ? zf.data() : nullptr, K ? idf.data() : nullptr, K, Kn ? zn.data() : nullptr, Kn,
-                                sim.Re, g3p, unif.data(), &did, nullptr);
+                                sim.Re, g3p, unif.data(), &did, &neff);
             if (rc != SLAMGPU_OK) break;
+            static const bool diag = getenv("SLAM_HOST_DIAG") != nullptr;  // nEff / decision per update (debug aid)
+            if (diag) {
+                fprintf(stderr, "[diag] it %u K %d Kn %d nEff %g did %d\n", sim.currentIteration, K, Kn, neff, did);
+                static bool reported = false;
+                slamgpu_debug_capture(h, 1);
+                if (neff != neff && !reported) {  // the weights this resample saw: all zero, or a NaN somewhere?
+                    reported = true;
+                    std::vector<float> wb((size_t) P);
+                    if (slamgpu_debug_read(h, SLAMGPU_DEBUG_W_BEFORE, wb.data()) == SLAMGPU_OK) {
+                        int zeros = 0, nans = 0, infs = 0;
+                        float mx = 0;
+                        for (float v : wb) {
+                            zeros += v == 0.0f;
+                            nans += v != v;
+                            infs += (v - v) != 0.0f && v == v;
+                            if (v == v && v > mx) mx = v;
+                        }
+                        fprintf(stderr, "[diag] weights entering the resample: %d zero, %d NaN, %d inf, max %g of %lld\n",
+                                zeros, nans, infs, mx, (long long) P);
+                    }
+                }
+            }
             res.observations++;
             res.resamples += did;
         }

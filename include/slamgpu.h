@@ -75,12 +75,15 @@ typedef struct slamgpu_config {
     int32_t device;      /* CUDA device ordinal */
     int32_t spare_rows;  /* free physical landmark rows for deferred gathers (0 = default: min(64, nf_cap)) */
     int32_t math_mode;   /* SLAMGPU_MATH_* */
-    int32_t log_epochs;  /* resamples whose keep[] is retained for deferred map gathers (0 = default 64) */
-    int32_t reserved[2];
+    int32_t log_epochs;  /* resamples whose keep[] is retained for deferred map gathers (0 = default 256) */
+    int32_t keep_nan_weights; /* 0 (default): a zero / non-finite weight sum (every likelihood underflowed) sets w = 1/N and
+                               * skips that resample, counted by SLAMGPU_STAT_WEIGHT_RESETS; 1: the reference's behaviour
+                               * (core.cpp:727-729 divides by the sum: NaN weights, nEff NaN, no resample ever again) */
+    int32_t reserved[1];
 } slamgpu_config;
 
 const char *slamgpu_last_error(void);
-/* Library / build identification, e.g. "slamgpu 0.1 sm_100a". */
+/* Library / build identification, e.g. "slamgpu 0.2 sm_100a". */
 const char *slamgpu_version(void);
 
 /* Replaces AcceleratorHandler::AcceleratorHandler / ~AcceleratorHandler (AcceleratorHandler.cpp:13-47):
@@ -210,6 +213,7 @@ int slamgpu_timing_reset(slamgpu_t *h);
 #define SLAMGPU_STAT_REMOTE_SOURCES 4 /* sharded: resampled slots whose particle came from another device */
 #define SLAMGPU_STAT_ROWS_FUSED 3 /* of ROWS_MOVED: re-columned inside the FastSLAM2 update kernel itself (no extra pass) */
 #define SLAMGPU_STAT_KEEP_FALLBACKS 5 /* resamples whose keep[] came from the exact sequential merge (core.cpp:800-806) */
+#define SLAMGPU_STAT_WEIGHT_RESETS 6 /* resamples that met a zero / non-finite weight sum (see keep_nan_weights) */
 int64_t slamgpu_stat(slamgpu_t *h, int32_t which);
 /* Total kernel launches issued by this handle since creation. */
 int64_t slamgpu_launch_count(slamgpu_t *h);

@@ -32,7 +32,8 @@ class Config(C.Structure):
     _fields_ = [("n_particles", C.c_int64), ("nf_cap", C.c_int32), ("method", C.c_int32), ("wheel_base", C.c_float),
                 ("sigma_phi", C.c_float), ("n_effective", C.c_int32), ("use_heading", C.c_int32),
                 ("do_resample", C.c_int32), ("scan_mode", C.c_int32), ("device", C.c_int32), ("spare_rows", C.c_int32),
-                ("math_mode", C.c_int32), ("log_epochs", C.c_int32), ("reserved", C.c_int32 * 2)]
+                ("math_mode", C.c_int32), ("log_epochs", C.c_int32), ("keep_nan_weights", C.c_int32),
+                ("reserved", C.c_int32 * 1)]
 
 
 _lib = None

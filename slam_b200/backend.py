@@ -40,7 +40,8 @@ class FastSLAM:
     """One FastSLAM1/FastSLAM2 particle set on one CUDA device."""
 
     def __init__(self, method, n_particles, nf_cap, wheel_base=4.0, sigma_phi=0.0, n_effective=None, use_heading=False,
-                 resample=True, scan_mode=SCAN_BLOCKED, device=0, spare_rows=0, math_mode=MATH_FAST, log_epochs=0):
+                 resample=True, scan_mode=SCAN_BLOCKED, device=0, spare_rows=0, math_mode=MATH_FAST, log_epochs=0,
+                 keep_nan_weights=False):
         self._L = _lib.load()
         self._h = C.c_void_p()
         self.P = int(n_particles)
@@ -60,6 +61,7 @@ class FastSLAM:
         cfg.spare_rows = spare_rows
         cfg.math_mode = math_mode
         cfg.log_epochs = log_epochs
+        cfg.keep_nan_weights = int(bool(keep_nan_weights))
         self._check(self._L.slamgpu_create(C.byref(cfg), C.byref(self._h)))
 
     # -- plumbing ---------------------------------------------------------------
@@ -96,7 +98,8 @@ class FastSLAM:
         """rows re-columned by deferred resampling, resamples applied, ancestor-chain steps."""
         return dict(rows_moved=self._L.slamgpu_stat(self._h, 0), resamples=self._L.slamgpu_stat(self._h, 1),
                     chain_steps=self._L.slamgpu_stat(self._h, 2), rows_fused=self._L.slamgpu_stat(self._h, 3),
-                    remote_sources=self._L.slamgpu_stat(self._h, 4), keep_fallbacks=self._L.slamgpu_stat(self._h, 5))
+                    remote_sources=self._L.slamgpu_stat(self._h, 4), keep_fallbacks=self._L.slamgpu_stat(self._h, 5),
+                    weight_resets=self._L.slamgpu_stat(self._h, 6))
 
     def seed(self, seed, predict_noise=False):
         """Throughput mode: noise the reference draws inside predict/update comes from the device generator."""

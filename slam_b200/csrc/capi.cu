@@ -314,6 +314,7 @@ extern "C" int64_t slamgpu_stat(slamgpu_t *h, int32_t which) {
         case SLAMGPU_STAT_ROWS_FUSED: return h->stat_rows_fused;
         case SLAMGPU_STAT_REMOTE_SOURCES: return (int64_t) h->h_sc->remote_sources;  // as of the last read-back
         case SLAMGPU_STAT_KEEP_FALLBACKS: return h->stat_keep_fallbacks;
+        case SLAMGPU_STAT_WEIGHT_RESETS: return (int64_t) h->h_sc->weight_resets;  // as of the last read-back
     }
     return 0;
 }
@@ -778,7 +779,8 @@ static int plan_fused_remap(slamgpu *h, const int *idf, int K, std::vector<int> 
         // (a landmark coming into view on a step that follows no resample) the REMAP instantiation of the update kernel
         // would cost more than it saves: it carries ~25 more instructions per particle-landmark for ALL K rows (~30 us at
         // cfg 4), a separate re-column pass ~12 us per row.
-        const bool fuse = (int) h->free_rows.size() >= n_stale && n_stale >= SLAM_REMAP_MIN_ROWS;
+        static const int min_rows = getenv("SLAMGPU_REMAP_MIN_ROWS") ? atoi(getenv("SLAMGPU_REMAP_MIN_ROWS")) : SLAM_REMAP_MIN_ROWS;
+        const bool fuse = (int) h->free_rows.size() >= n_stale && n_stale >= min_rows;
         for (int i = 0; i < K; i++) {
             const long long re = h->row_epoch[idf[i]];
             if (re < h->epoch && (!fuse || re != e)) others.push_back(idf[i]);
@@ -1004,7 +1006,8 @@ static int resample_indices(slamgpu *h, const UnifChoice &uc) {
             LAUNCHED(h, SLAMGPU_T_WEIGHTS);
         }
         k_reference_weights<<<1, 1, 0, h->stream>>>(h->w, P, h->di(), h->unif(), k, khalf, h->mloc, h->cdf, h->sel, d,
-                                                    (float) h->cfg.n_effective, h->cfg.do_resample);
+                                                    (float) h->cfg.n_effective, h->cfg.do_resample,
+                                                    h->cfg.keep_nan_weights);
         KCHECK();
         LAUNCHED(h, SLAMGPU_T_WEIGHTS);
         k_keep_sequential<<<1, 1, 0, h->stream>>>(h->sel, h->cdf, h->keep, P);
@@ -1028,6 +1031,8 @@ static int resample_indices(slamgpu *h, const UnifChoice &uc) {
     wa.sc = d;
     wa.neff_threshold = (float) h->cfg.n_effective;
     wa.do_resample = h->cfg.do_resample;
+    wa.uniform_w = 1.0f / (float) Pg;
+    wa.keep_nan = h->cfg.keep_nan_weights;
     const int arr1[1] = {0}, arr2[3] = {1, 2, 3};
     const bool halo = !uc.rng;  // the generator can produce any slot's uniform anywhere: nothing to send
     if (h->world > 1 && h->log_pending) {

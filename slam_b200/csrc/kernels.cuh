@@ -711,7 +711,19 @@ struct WeightsArgs {
     Scalars *sc;
     float neff_threshold;                  // (float) NEFFECTIVE
     int do_resample;
+    float uniform_w;                       // 1 / N over the GLOBAL particle count
+    int keep_nan;                          // 1: the reference's behaviour on a zero weight sum (NaN weights for good)
 };
+
+// A weight sum that is zero or not finite: every particle's likelihood underflowed (a loop closure the whole cloud
+// disagrees with, 100 particles and a 1-degree bearing sigma: seen on BASELINE.json config 0) or something overflowed.
+// The reference divides by it (core.cpp:727-729): every weight becomes NaN, nEff is NaN, `nEff < NEFFECTIVE` is false
+// for ever after and the filter never resamples again.  Unless asked for exactly that (slamgpu_config.keep_nan_weights)
+// the library carries the particle set on UNWEIGHTED instead: w = 1/N, nEff = N, no resample this step, and counts the
+// event (SLAMGPU_STAT_WEIGHT_RESETS).  Every CTA and every rank sees the same sum, so all take the same branch.
+__device__ __forceinline__ bool weights_degenerate(const WeightsArgs &a, float ws) {
+    return !a.keep_nan && !(ws > 0.0f && ws <= 3.0e38f);
+}
 
 __device__ __forceinline__ void weights_phase_a(const WeightsArgs &a, int lb, float *sh) {
     const size_t i = (size_t) lb * SLAM_SCAN_BLOCK + threadIdx.x;
@@ -727,7 +739,7 @@ __device__ __forceinline__ void weights_phase_c(const WeightsArgs &a, int lb, fl
     const size_t i = (size_t) lb * SLAM_SCAN_BLOCK + threadIdx.x;
     float wn = 0.0f;
     if (i < a.n) {
-        wn = __fdiv_rn(a.w[i], ws);
+        wn = weights_degenerate(a, ws) ? a.uniform_w : __fdiv_rn(a.w[i], ws);
         a.w[i] = wn;
     }
     const float sq = __fmul_rn(wn, wn);
@@ -820,6 +832,7 @@ __device__ __forceinline__ void weights_phase_d(const WeightsArgs &a, int which,
         if (threadIdx.x == 0) {
             a.sc->ws = ws;
             a.sc->csum = csum;
+            if (weights_degenerate(a, ws)) a.sc->weight_resets++;
         }
     } else {
         const float s2 = upper_total(a.tot_s, n, sh, chunk_tot, bcast);
@@ -1185,11 +1198,13 @@ __device__ float eigen_sum_seq(const float *v, long n) {
 __global__ void k_reference_weights(float *__restrict__ w, size_t n, const float *__restrict__ di,
                                     const double *__restrict__ unif, float k, float khalf, float *__restrict__ sq,
                                     float *__restrict__ cdf, float *__restrict__ sel, Scalars *__restrict__ sc,
-                                    float neff_threshold, int do_resample) {
+                                    float neff_threshold, int do_resample, int keep_nan) {
     if (blockIdx.x != 0 || threadIdx.x != 0) return;
     const float ws = eigen_sum_seq(w, (long) n);
+    const bool degenerate = !keep_nan && !(ws > 0.0f && ws <= 3.0e38f);  // see weights_degenerate()
+    if (degenerate) sc->weight_resets++;
     for (size_t i = 0; i < n; i++) {
-        const float wn = __fdiv_rn(w[i], ws);
+        const float wn = degenerate ? (float) (1.0 / (double) n) : __fdiv_rn(w[i], ws);
         w[i] = wn;
         sq[i] = __fmul_rn(wn, wn);
     }

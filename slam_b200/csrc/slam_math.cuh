@@ -418,8 +418,8 @@ SLAM_HD void fs1_weight_and_feature_update(const float *x, const float *R, float
 // =============================================================================================================
 // MUFU approximations issued directly (rsqrt/rcp/ex2 .approx.ftz): rsqrtf(), __fdividef() and __expf() without
 // -ftz wrap the same MUFU instruction in a denormal-range test and two rescaling multiplies (3-5 extra instructions
-// each, 11 such calls per particle-landmark: ncu r01, profiles/).  Denormal inputs cannot occur here (ranges,
-// variances and determinants of metre-scale quantities); a likelihood factor below 2^-126 flushes to zero.
+// each, 11 such calls per particle-landmark: ncu r01, profiles/).  Denormal inputs cannot occur for rsqrt / rcp here
+// (ranges, variances and determinants of metre-scale quantities); ex2 is the exception, see mufu_ex2.
 #if defined(__CUDA_ARCH__)
 __device__ __forceinline__ float mufu_rsqrt(float x) {
     float r;
@@ -431,9 +431,14 @@ __device__ __forceinline__ float mufu_rcp(float x) {
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
+// NOT flushed to zero: a likelihood below 2^-126 stays a denormal like the reference's expf result.  That matters
+// exactly when a filter is in trouble — every particle far from the observations: with a flush all weights become 0,
+// their sum 0, the normalised weights NaN and nEff NaN, so nothing ever resamples again, whereas the reference keeps
+// a denormal weight on the least bad particle, resamples onto it and recovers (seen as two lost tracks in 37 seeded
+// runs of BASELINE.json config 0 with the flushing version, none in 41 without).  Costs two scaling instructions.
 __device__ __forceinline__ float mufu_ex2(float x) {
     float r;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    asm("ex2.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
 #define SLAM_RSQRT(x) mufu_rsqrt(x)

@@ -111,7 +111,8 @@ struct Scalars {
     int comm_error;                     // sticky: a peer never arrived at an exchange (cleared only after it was reported)
     unsigned long long remote_sources;  // resampled slots whose particle came from another device (running total)
     int gauss_late;                     // sticky: a chunk of an in-flight noise upload never arrived (GaussArrival)
-    int pad[7];
+    int weight_resets;                  // resamples that met a zero / non-finite weight sum and went on unweighted
+    int pad[6];
 };
 
 // Grid-wide barrier of the cooperative weights kernel: a counter that only ever grows; `base` is its value before the

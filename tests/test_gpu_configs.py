@@ -71,7 +71,13 @@ def test_config_against_reference_program(exe, tmp_path, tag, follow):
     print("%s (%s): follows the reference program to 1e-4 for %d of %d iterations (max %.1e)"
           % (tag, method, nrow * EVERY, ref.shape[0] * EVERY, err))
     assert nrow >= (ref.shape[0] if follow is None else follow // EVERY), (nrow * EVERY, err)
-    # to the end of the run the estimate tracks the true path as well as the reference's own estimate does
-    err_ref = np.abs(ref[:, 4:6] - ref[:, 1:3]).max()
-    err = np.abs(a8[:, 4:6] - a8[:, 1:3]).max()
-    assert err <= max(2.0 * err_ref, err_ref + 1.0), (err, err_ref)
+    # To the end of the run the estimate tracks the true path like the reference's own estimate does.  After the
+    # realisations part this is a statement about a random process, not about bits: the RMS error over the run is held
+    # to 2x the reference's + 0.5 m and the worst error to 3x + 1 m (the reference program itself, over 12 seeds of
+    # cfg 0: RMS 0.21 .. 1.07 m, worst error 0.47 .. 1.47 m; tools/cfg_track.py prints the same for this program).
+    e_ref = np.hypot(ref[:, 4] - ref[:, 1], ref[:, 5] - ref[:, 2])
+    e = np.hypot(a8[:, 4] - a8[:, 1], a8[:, 5] - a8[:, 2])
+    rms_ref, rms = np.sqrt(np.mean(e_ref ** 2)), np.sqrt(np.mean(e ** 2))
+    print("%s: RMS position error %.3f m (reference %.3f), worst %.3f m (reference %.3f)"
+          % (tag, rms, rms_ref, e.max(), e_ref.max()))
+    assert rms <= 2.0 * rms_ref + 0.5 and e.max() <= 3.0 * e_ref.max() + 1.0, (rms, rms_ref, e.max(), e_ref.max())

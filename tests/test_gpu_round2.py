@@ -411,3 +411,29 @@ def test_comm_init_rejects_more_than_2_30_particles(sb):
         f.comm_init(0, 8, bytes(128))
     assert e.value.code == -1 and "2^30" in str(e.value)
     f.close()
+
+
+@pytest.mark.parametrize("scan", ["blocked", "reference"])
+def test_zero_weight_sum_goes_on_unweighted(sb, scan):
+    """Every likelihood underflowed (BASELINE.json config 0 does that at a loop closure with the shipped seed: 100
+    particles, 1-degree bearing sigma): the reference divides by the zero sum (core.cpp:727-729) and is left with NaN
+    weights and a NaN nEff for good.  By default the library sets w = 1/N, reports nEff = N, skips that resample and
+    counts the event; keep_nan_weights = 1 asks for the reference's behaviour."""
+    N = 3000
+    mode = sb.SCAN_BLOCKED if scan == "blocked" else sb.SCAN_REFERENCE
+    unif = np.random.default_rng(0).random(N)
+    f = sb.FastSLAM(sb.FASTSLAM1, N, 4, n_effective=int(0.75 * N), scan_mode=mode)
+    f.upload(w=np.zeros(N, np.float32))
+    keep, neff, did = f.resample(unif, want_keep=True)
+    assert not did and neff == float(N)
+    assert np.all(f.download(landmarks=False)["w"] == np.float32(1.0 / N))
+    assert f.stats()["weight_resets"] == 1
+    f.upload(w=np.full(N, 2.0, np.float32))                       # and an ordinary sum afterwards
+    keep, neff, did = f.resample(unif, want_keep=True)
+    assert neff == pytest.approx(N, rel=1e-5) and f.stats()["weight_resets"] == 1
+    f.close()
+    f = sb.FastSLAM(sb.FASTSLAM1, N, 4, n_effective=int(0.75 * N), scan_mode=mode, keep_nan_weights=True)
+    f.upload(w=np.zeros(N, np.float32))
+    keep, neff, did = f.resample(unif, want_keep=True)
+    assert not did and np.isnan(neff) and np.isnan(f.download(landmarks=False)["w"]).all()
+    f.close()
