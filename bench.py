@@ -50,6 +50,7 @@ def parse():
     ap.add_argument("--ref-particles", type=int, default=1000, help="particles per reference instance (core.cpp:762 valid)")
     ap.add_argument("--burn-in", type=int, default=100, help="untimed steps before the timed (steady-state) leg")
     ap.add_argument("--no-parity", action="store_true", help="skip the untimed oracle parity phase")
+    ap.add_argument("--parity-landmarks", type=int, default=40, help="landmarks per particle in the parity phase")
     ap.add_argument("--no-config5", action="store_true", help="N > 1: skip the secondary 4096-landmark leg")
     return ap.parse_args()
 
@@ -463,7 +464,7 @@ def roofline_of(res, peak, peak_src):
             "family_ms_per_step": {k: x["ms"] / max(1, res["value_steps"]) for k, x in fam.items()}}
 
 
-def parity_phase(cx, slam_b200):
+def parity_phase(cx, slam_b200, Nf=40):
     """Untimed: N ranks x 4096 particles x 40 landmarks x 8 observations through slamgpu_update (fused re-columning,
     in-kernel exchanges, migration over peer memory), weights skewed so that a large part of every resample's sources
     sits on another rank, compared on rank 0 with the ORACLE run in one piece: keep[], nEff, the decision and the
@@ -474,7 +475,7 @@ def parity_phase(cx, slam_b200):
     from oracle.pyoracle import Oracle, State
     from replay import compare_states, snapshot
     dist, world, rank = cx.dist, cx.world, cx.rank
-    Pl, Nf, K, CYCLES = 4096, 40, 8, 4
+    Pl, K, CYCLES = 4096, 8, 4
     Pg = Pl * world
     d = synthetic_state(Pg, Nf, K, seed=21, extent=40.0)
     n_eff = int(0.75 * Pg)
@@ -614,7 +615,7 @@ def run_ours(a):
               "rows_recolumned": r5["value"]["stats"]["rows_moved"], "resamples": r5["value"]["stats"]["resamples"],
               "update_frac_of_hbm": rf5["families"].get("update", {}).get("frac"),
               "family_ms_per_step": rf5["family_ms_per_step"], "remote_fraction": r5["remote_frac"]}
-    parity, parity_ok = (None, True) if a.no_parity else parity_phase(cx, slam_b200)
+    parity, parity_ok = (None, True) if a.no_parity else parity_phase(cx, slam_b200, a.parity_landmarks)
 
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
