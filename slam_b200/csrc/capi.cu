@@ -225,8 +225,9 @@ static int create_impl(const slamgpu_config *cfg, slamgpu *h) {
     h->force_anomaly = getenv("SLAMGPU_FORCE_ANOMALY") != nullptr;
     {   // the FastSLAM2 fast kernels stage up to 2048 observations next to their landmark ring: > 48 KB
         const int big = (int) SLAM_FS2_FAST_SMEM(2048);
-        CU(cudaFuncSetAttribute(k_fs2_update_fast<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-        CU(cudaFuncSetAttribute(k_fs2_update_fast<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        CU(cudaFuncSetAttribute(k_fs2_update_fast<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        CU(cudaFuncSetAttribute(k_fs2_update_fast<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        CU(cudaFuncSetAttribute(k_fs2_update_fast<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
         CU(cudaFuncSetAttribute(k_fs2_update_listed<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
         CU(cudaFuncSetAttribute(k_fs2_update_listed<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     }
@@ -924,8 +925,14 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
                 ga.late = &h->d_sc->gauss_late;
             }
             if (anc) {
-                k_fs2_update_fast<true><<<grid, SLAM_UPDATE_THREADS, sm_f, h->stream>>>(
-                    h->soa(h->cur), h->ring(), P, o, K, Rm, noise, ga, anc, pr, Pgl, h->fb_list, h->fb_count);
+                bool all_stale = true;  // the step after a resample: every observed row is read at the ancestor's column
+                for (int i = 0; i < K; i++) all_stale = all_stale && rows[i] != dst[i];
+                if (all_stale)
+                    k_fs2_update_fast<2><<<grid, SLAM_UPDATE_THREADS, sm_f, h->stream>>>(
+                        h->soa(h->cur), h->ring(), P, o, K, Rm, noise, ga, anc, pr, Pgl, h->fb_list, h->fb_count);
+                else
+                    k_fs2_update_fast<1><<<grid, SLAM_UPDATE_THREADS, sm_f, h->stream>>>(
+                        h->soa(h->cur), h->ring(), P, o, K, Rm, noise, ga, anc, pr, Pgl, h->fb_list, h->fb_count);
                 KCHECK();
                 LAUNCHED(h, SLAMGPU_T_UPDATE);
                 if (gauss_in_kernel) {  // the fallback-list kernel (and anything later) reads the whole buffer
@@ -935,7 +942,7 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
                 k_fs2_update_listed<true><<<grid_l, 128, sm_l, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, noise,
                                                                             anc, pr, Pgl, h->fb_list, h->fb_count);
             } else {
-                k_fs2_update_fast<false><<<grid, SLAM_UPDATE_THREADS, sm_f, h->stream>>>(
+                k_fs2_update_fast<0><<<grid, SLAM_UPDATE_THREADS, sm_f, h->stream>>>(
                     h->soa(h->cur), h->ring(), P, o, K, Rm, noise, ga, nullptr, pr, Pgl, h->fb_list, h->fb_count);
                 KCHECK();
                 LAUNCHED(h, SLAMGPU_T_UPDATE);

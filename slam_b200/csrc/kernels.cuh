@@ -392,7 +392,9 @@ __device__ __forceinline__ void gauss_arrived_load(const GaussArrival &ga, const
     }
 }
 
-template <bool REMAP>
+// REMAP: 0 = every observed row is current; 1 = some are stale (checked per row: soff != doff); 2 = ALL K are stale —
+// the step after a resample, the common case — so the per-row check and the second pair of copies drop out.
+template <int REMAP>
 __global__ void __launch_bounds__(SLAM_UPDATE_THREADS, 7) k_fs2_update_fast(PoseSoA s, MapRing m, size_t P, ObsSet o, int K,
                                                                          float4 Rm, const NoiseSrc noise, GaussArrival ga,
                                                                          const int *__restrict__ anc, PeerRows pr,
@@ -403,7 +405,7 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS, 7) k_fs2_update_fast(Pose
     float2 *const ring_mean = reinterpret_cast<float2 *>(reinterpret_cast<float4 *>(slam_smem) + D * T) + threadIdx.x;
     float2 *sz, *ssc;
     unsigned long long *soff, *doff;
-    stage_obs_fs2<REMAP>(slam_smem + (sizeof(float4) + sizeof(float2)) * D * T, o, K, P, sz, soff, doff, ssc);
+    stage_obs_fs2<(REMAP != 0)>(slam_smem + (sizeof(float4) + sizeof(float2)) * D * T, o, K, P, sz, soff, doff, ssc);
     const unsigned blk = REMAP ? spread_block(blockIdx.x, gridDim.x, pr.spread, SLAM_SPREAD_CHUNK_SLOTS / T) : blockIdx.x;
     const size_t p = (size_t) blk * blockDim.x + threadIdx.x;
     if (p >= P) return;
@@ -416,7 +418,7 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS, 7) k_fs2_update_fast(Pose
     // row i goes in flight into ring slot `slot`: its own column, or (stale) the ancestor's, then through L1 as well
     auto fetch = [&](int i, int slot) {
         const unsigned long long so = soff[i];
-        if (REMAP && so != doff[i]) {
+        if (REMAP == 2 || (REMAP == 1 && so != doff[i])) {
             cp_async_8(ring_mean + slot * T, smean + so);
             cp_async_16_ca(ring_cov + slot * T, scov + so);
         } else {

@@ -80,11 +80,13 @@ def test_committed_cuda_line_carries_the_contract():
 def test_committed_multi_gpu_lines_carry_parity():
     """Every committed N > 1 line carries the oracle parity phase run at that rank count."""
     files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r02_bench_[2-8]gpu.json")))
+    assert any("config5" in json_lines(open(f).read())[-1] for f in files)
     for f in files:
         d = json_lines(open(f).read())[-1]
         p = d["parity"]
         assert p["ranks"] == d["n_gpus"] and p["ok"] and p["keep_bit_exact"] and p["remote_fraction"] > 0.3, f
-        assert d["config5"]["map_bytes_per_gpu"] > 100e9, f
+        if "config5" in d:  # the 4096-landmark leg (run at 8 ranks; --no-config5 at 2 and 4)
+            assert d["config5"]["map_bytes_per_gpu"] > 100e9, f
 
 
 def test_cuda_arm_fails_loudly_without_a_gpu():
