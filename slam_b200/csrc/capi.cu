@@ -209,7 +209,7 @@ static int create_impl(const slamgpu_config *cfg, slamgpu *h) {
     CU(cudaHostAlloc(&h->h_sc, sizeof(Scalars), cudaHostAllocDefault));
     memset(h->h_sc, 0, sizeof(Scalars));
     h->est_blocks = 148 * 4;
-    CU(cudaMalloc(&h->d_est, sizeof(EstPartial) * h->est_blocks));
+    CU(cudaMalloc(&h->d_est, sizeof(EstPartial) * std::max<size_t>(h->est_blocks, grid_for(P, 256))));
     CU(cudaMalloc(&h->est_ticket, sizeof(unsigned)));
     CU(cudaMemset(h->est_ticket, 0, sizeof(unsigned)));
     CU(cudaMalloc(&h->d_tail, sizeof(TailBlob)));
@@ -1137,6 +1137,25 @@ static int launch_gather_pose(slamgpu *h, const int *cond) {
     return SLAMGPU_OK;
 }
 
+// The speculative tail of a resample in one launch: conditional pose gather + pose estimate (k_gather_pose_estimate).
+static int launch_gather_estimate(slamgpu *h, const int *cond) {
+    const size_t P = h->P, Pg = h->Pg;
+    const float new_w = 1.0f / (float) Pg;
+    PeerMaps pm;
+    RET(peer_maps(h, &pm));
+    RET(order_pose(h, h->cur ^ 1, h->cur));  // see launch_gather_pose
+    int *slot = h->keeplog + (size_t) ((h->epoch + 1) % h->H) * Pg;
+    TimedSpan sg;
+    RET(span_begin(h, SLAMGPU_T_GATHER, &sg));
+    k_gather_pose_estimate<<<grid_for(P, 256), 256, 0, h->stream>>>(
+        pm, h->cur, h->pose[h->cur ^ 1], h->w, h->keep, P, (long long) Pg, new_w, h->rank, &h->d_sc->remote_sources,
+        h->world > 1 ? nullptr : slot, cond, (long long) h->slot0, h->d_est, h->est_ticket, &h->d_tail->est);
+    KCHECK();
+    LAUNCHED(h, SLAMGPU_T_GATHER);
+    RET(span_end(h, &sg));
+    return SLAMGPU_OK;
+}
+
 // K8 into the tail record.  pick: device flag selecting the freshly gathered pose buffer (nullptr: the current one).
 static int launch_estimate(slamgpu *h, const int *pick) {
     TimedSpan sp;
@@ -1345,8 +1364,8 @@ extern "C" int slamgpu_resample(slamgpu_t *h, const double *unif, int32_t *keep_
     // sitting between two launches, and slamgpu_estimate right after an update costs neither a launch nor a second
     // synchronisation.
     const int *cond = h->cfg.do_resample ? &h->d_sc->did : nullptr;
-    if (cond) RET(launch_gather_pose(h, cond));
-    RET(launch_estimate(h, cond));
+    if (cond) RET(launch_gather_estimate(h, cond));
+    else RET(launch_estimate(h, nullptr));
     RET(fetch_tail(h));
     CU(cudaStreamSynchronize(h->stream));
     h->gauss_chunked = false;

@@ -1456,6 +1456,79 @@ __global__ void __launch_bounds__(256) k_estimate(const float *__restrict__ xv_a
     }
 }
 
+// The resample's tail in ONE launch: the conditional pose gather of k_gather_pose and the pose estimate of k_estimate.
+// Every thread holds the (x, y, weight) its slot ends up with — the gathered particle's when the device-side decision
+// (cond) says resample, its own otherwise — so the estimate's reduction runs on registers instead of re-reading 12 B
+// per particle in a second kernel.  grid = ceil(P / 256); part holds one partial per CTA.
+__global__ void __launch_bounds__(256) k_gather_pose_estimate(PeerMaps pm, int cur, float *__restrict__ dst_pose,
+                                                              float *__restrict__ w, const int *__restrict__ keep,
+                                                              size_t P, long long n_global, float new_w, int rank,
+                                                              unsigned long long *__restrict__ remote_sources,
+                                                              int *__restrict__ log_slot, const int *__restrict__ cond,
+                                                              long long offset, EstPartial *part, unsigned *ticket,
+                                                              EstPartial *__restrict__ out) {
+    __shared__ bool last;
+    const bool resample = *cond != 0;
+    const size_t p = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const float *own = pm.pose[cur][pm.world > 1 ? rank : 0];
+    int remote = 0;
+    EstPartial v;
+    v.sx = 0; v.sy = 0; v.wmax = -INFINITY; v.imax = 0x7fffffffffffffffLL;
+    if (p < P) {
+        if (resample) {
+            long long k = keep[p];
+            if (log_slot) log_slot[p] = (int) k;
+            if (k < 0) k = n_global - 1;
+            const int r = (pm.world > 1) ? (int) (k / (long long) P) : 0;
+            const size_t sidx = (size_t) (k - (long long) r * (long long) P);
+            const float *src = pm.pose[cur][r];
+            float val[12];
+#pragma unroll
+            for (int c = 0; c < 12; c++) val[c] = src[c * P + sidx];
+#pragma unroll
+            for (int c = 0; c < 12; c++) dst_pose[c * P + p] = val[c];
+            w[p] = new_w;
+            remote = (pm.world > 1 && r != rank);
+            v.sx = val[0];
+            v.sy = val[1];
+            v.wmax = new_w;
+        } else {
+            v.sx = own[p];
+            v.sy = own[P + p];
+            v.wmax = w[p];
+        }
+        v.imax = offset + (long long) p;
+    }
+    if (pm.world > 1 && resample) {
+        const int n = __syncthreads_count(remote);
+        if (threadIdx.x == 0 && n) atomicAdd(remote_sources, (unsigned long long) n);
+    }
+    v = est_block_reduce(v);
+    if (threadIdx.x == 0) {
+        part[blockIdx.x] = v;
+        __threadfence();
+        last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    v.sx = 0; v.sy = 0; v.wmax = -INFINITY; v.imax = 0x7fffffffffffffffLL;
+    for (int i = threadIdx.x; i < (int) gridDim.x; i += blockDim.x) {
+        const volatile EstPartial *q = part + i;  // written by other CTAs of this launch
+        EstPartial o;
+        o.sx = q->sx; o.sy = q->sy; o.wmax = q->wmax; o.theta = 0.0f; o.imax = q->imax;
+        est_combine(v, o);
+    }
+    v = est_block_reduce(v);
+    if (threadIdx.x == 0) {
+        const long long loc = v.imax - offset;
+        const float *heading = (resample ? dst_pose : own) + 2 * P;  // dst_pose: written by other CTAs of this launch
+        v.theta = (loc >= 0 && loc < (long long) P) ? __ldcg(heading + (size_t) loc) : 0.0f;
+        *out = v;
+        *ticket = 0;
+    }
+}
+
 // Strided download helper: every stride-th particle's pose and landmark means, packed.
 __global__ void __launch_bounds__(256) k_decimate(PoseSoA s, MapRing m, size_t P, size_t stride, size_t n, int Nf,
                                                   const int *__restrict__ phys, float *__restrict__ xv_out,
