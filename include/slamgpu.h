@@ -169,6 +169,20 @@ int slamgpu_compute_jacobians_batch(slamgpu_t *h, const int32_t *idf, int32_t K,
 /* ParticleSLAMWrapper::computeEstimatedPosition (ParticleSLAMWrapper.cpp:56-77): mean x, mean y (double
  * accumulation) and the heading of the first maximum-weight particle. */
 int slamgpu_estimate(slamgpu_t *h, double *x, double *y, double *t);
+/* The same estimate WITHOUT a handle and without allocating anything, for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  It has no counterpart in the reference.
+ * The kernel's scratch (per-CTA partials + ticket, 33 KB) is a
+ * static __device__ array that every GPU loading the library holds until exit; it bounds the call at
+ * SLAMGPU_NOALLOC_MAX_PARTICLES, beyond which the call fails with SLAMGPU_EINVAL.  Runs on the CURRENT device.
+ *   d_xv  : DEVICE memory, [3][n_particles] floats: the rows x, y, theta
+ *   d_w   : DEVICE memory, [n_particles] weights
+ *   d_out : DEVICE memory, 4 doubles: mean x, mean y, heading of the first maximum-weight particle, that weight
+ *   cuda_stream : a cudaStream_t (NULL = the default stream); the result is ready when the stream reaches that point
+ * No cudaMalloc / cudaFree / allocating routine is called (one cudaGetSymbolAddress the first time a device is used,
+ * one 4-byte cudaMemsetAsync and one kernel per call).  All calls on a device share the scratch: calls that overlap
+ * on the GPU (different streams, no ordering between them) race; serialise them. */
+#define SLAMGPU_NOALLOC_MAX_PARTICLES (1 << 22)
+int slamgpu_estimate_noalloc(const float *d_xv, const float *d_w, int64_t n_particles, double *d_out, void *cuda_stream);
 /* Every stride-th particle's pose (and optionally its first Nf landmark means) for the plot feed
  * (ParticleSLAMWrapper.cpp:34-54 sends all of them; that cannot scale to 1M particles).
  * xv_out [3][n], lm_out [Nf][n][2] (nullable), n = ceil(P/stride). */

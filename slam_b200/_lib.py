@@ -15,7 +15,7 @@ EXPORTS = [
     "slamgpu_compute_jacobians", "slamgpu_compute_jacobians_batch", "slamgpu_estimate", "slamgpu_download_decimated",
     "slamgpu_timing_enable", "slamgpu_timing_read", "slamgpu_timing_reset", "slamgpu_launch_count", "slamgpu_stat",
     "slamgpu_comm_unique_id", "slamgpu_comm_init", "slamgpu_update_i32", "slamgpu_seed", "slamgpu_download_slice",
-    "slamgpu_debug_capture", "slamgpu_debug_read", "slamgpu_download_poses_at",
+    "slamgpu_debug_capture", "slamgpu_debug_read", "slamgpu_download_poses_at", "slamgpu_estimate_noalloc",
     "slamgpu_ekf_create", "slamgpu_ekf_destroy", "slamgpu_ekf_sim", "slamgpu_ekf_size", "slamgpu_ekf_set_state",
     "slamgpu_ekf_get_state", "slamgpu_ekf_get_pose", "slamgpu_ekf_launch_count",
 ]
@@ -92,6 +92,7 @@ def load():
     L.slamgpu_compute_jacobians.argtypes = [vp, fp, C.c_int32, fp]
     L.slamgpu_compute_jacobians_batch.argtypes = [vp, ip, C.c_int32, fp, fp]
     L.slamgpu_estimate.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    L.slamgpu_estimate_noalloc.argtypes = [vp, vp, C.c_int64, vp, vp]
     L.slamgpu_download_decimated.argtypes = [vp, C.c_int64, fp, fp]
     L.slamgpu_timing_enable.argtypes = [vp, C.c_int32]
     L.slamgpu_timing_read.argtypes = [vp, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_int64),

@@ -291,3 +291,16 @@ def compute_jacobians(rec, n):
     if rc != 0:
         raise SlamGpuError(rc, L.slamgpu_last_error().decode())
     return out
+
+
+NOALLOC_MAX_PARTICLES = 1 << 22
+
+
+def estimate_noalloc(d_xv, d_w, n_particles, d_out, stream=0):
+    """slamgpu_estimate_noalloc (include/slamgpu.h): the pose estimate on DEVICE pointers (ints), nothing allocated.
+    d_xv [3][n] float32, d_w [n] float32, d_out 4 float64 — all device addresses on the current device; stream is a
+    cudaStream_t handle (0 = default stream).  No counterpart in the reference."""
+    L = _lib.load()
+    rc = L.slamgpu_estimate_noalloc(int(d_xv), int(d_w), int(n_particles), int(d_out), int(stream) or None)
+    if rc != 0:
+        raise SlamGpuError(rc, L.slamgpu_last_error().decode())

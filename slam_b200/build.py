@@ -7,7 +7,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libslamgpu.so")
-SOURCES = ["capi.cu", "comm.cu", "ekf.cu"]
+SOURCES = ["capi.cu", "comm.cu", "ekf.cu", "noalloc.cu"]
 HEADERS = ["slam_math.cuh", "slam_rng.cuh", "xchg.cuh", "kernels.cuh", "ekf_kernels.cuh", "types.cuh", "handle.h", os.path.join("..", "..", "include", "slamgpu.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
               "-shared"]
