@@ -225,9 +225,12 @@ static int create_impl(const slamgpu_config *cfg, slamgpu *h) {
     h->force_anomaly = getenv("SLAMGPU_FORCE_ANOMALY") != nullptr;
     {   // the FastSLAM2 fast kernels stage up to 2048 observations next to their landmark ring: > 48 KB
         const int big = (int) SLAM_FS2_FAST_SMEM(2048);
-        CU(cudaFuncSetAttribute(k_fs2_update_fast<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-        CU(cudaFuncSetAttribute(k_fs2_update_fast<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-        CU(cudaFuncSetAttribute(k_fs2_update_fast<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        CU(cudaFuncSetAttribute(k_fs2_update_fast<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        CU(cudaFuncSetAttribute(k_fs2_update_fast<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        CU(cudaFuncSetAttribute(k_fs2_update_fast<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        CU(cudaFuncSetAttribute(k_fs2_update_fast<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        CU(cudaFuncSetAttribute(k_fs2_update_fast<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        CU(cudaFuncSetAttribute(k_fs2_update_fast<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
         CU(cudaFuncSetAttribute(k_fs2_update_listed<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
         CU(cudaFuncSetAttribute(k_fs2_update_listed<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
     }
@@ -248,7 +251,9 @@ static int create_impl(const slamgpu_config *cfg, slamgpu *h) {
 extern "C" int slamgpu_create(const slamgpu_config *cfg, slamgpu_t **out) {
     if (!cfg || !out) return slam_fail(SLAMGPU_EINVAL, "null argument");
     *out = nullptr;
-    if (cfg->n_particles <= 0 || cfg->n_particles > (1ll << 30)) return slam_fail(SLAMGPU_EINVAL, "n_particles out of range");
+    // below 2^28 per device: the update kernel addresses a landmark row as base + row * (P * 16 bytes) with a 32-bit
+    // pitch (one row of one landmark would already be 4 GB there; 2^30 stays the bound on the GLOBAL count, comm_init)
+    if (cfg->n_particles <= 0 || cfg->n_particles >= (1ll << 28)) return slam_fail(SLAMGPU_EINVAL, "n_particles out of range");
     if (cfg->nf_cap <= 0) return slam_fail(SLAMGPU_EINVAL, "nf_cap must be positive");
     if (cfg->method != SLAMGPU_FASTSLAM1 && cfg->method != SLAMGPU_FASTSLAM2)
         return slam_fail(SLAMGPU_EINVAL, "method must be SLAMGPU_FASTSLAM1 or SLAMGPU_FASTSLAM2");
@@ -917,6 +922,8 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
         if (fs2 && fast) {
             const unsigned grid = grid_for(P, SLAM_UPDATE_THREADS), grid_l = std::min<unsigned>(grid, 148u * 4u);
             const size_t sm_f = SLAM_FS2_FAST_SMEM(K), sm_l = SLAM_OBS_FS2_SMEM(K);
+            // no ragged tail in the unrolled walk over the observations
+            const bool kfull = K >= SLAM_RING_DEPTH && K % SLAM_RING_DEPTH == 0;
             CU(cudaMemsetAsync(h->fb_count, 0, sizeof(int), h->stream));
             GaussArrival ga = {nullptr, 0, nullptr};
             if (gauss_in_kernel) {
@@ -927,12 +934,10 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
             if (anc) {
                 bool all_stale = true;  // the step after a resample: every observed row is read at the ancestor's column
                 for (int i = 0; i < K; i++) all_stale = all_stale && rows[i] != dst[i];
-                if (all_stale)
-                    k_fs2_update_fast<2><<<grid, SLAM_UPDATE_THREADS, sm_f, h->stream>>>(
-                        h->soa(h->cur), h->ring(), P, o, K, Rm, noise, ga, anc, pr, Pgl, h->fb_list, h->fb_count);
-                else
-                    k_fs2_update_fast<1><<<grid, SLAM_UPDATE_THREADS, sm_f, h->stream>>>(
-                        h->soa(h->cur), h->ring(), P, o, K, Rm, noise, ga, anc, pr, Pgl, h->fb_list, h->fb_count);
+                auto *kern = all_stale ? (kfull ? k_fs2_update_fast<2, true> : k_fs2_update_fast<2, false>)
+                                       : (kfull ? k_fs2_update_fast<1, true> : k_fs2_update_fast<1, false>);
+                kern<<<grid, SLAM_UPDATE_THREADS, sm_f, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, noise, ga, anc, pr,
+                                                                     Pgl, h->fb_list, h->fb_count);
                 KCHECK();
                 LAUNCHED(h, SLAMGPU_T_UPDATE);
                 if (gauss_in_kernel) {  // the fallback-list kernel (and anything later) reads the whole buffer
@@ -942,8 +947,9 @@ extern "C" int slamgpu_update_particles(slamgpu_t *h, const float *zf, const int
                 k_fs2_update_listed<true><<<grid_l, 128, sm_l, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, noise,
                                                                             anc, pr, Pgl, h->fb_list, h->fb_count);
             } else {
-                k_fs2_update_fast<0><<<grid, SLAM_UPDATE_THREADS, sm_f, h->stream>>>(
-                    h->soa(h->cur), h->ring(), P, o, K, Rm, noise, ga, nullptr, pr, Pgl, h->fb_list, h->fb_count);
+                auto *kern = kfull ? k_fs2_update_fast<0, true> : k_fs2_update_fast<0, false>;
+                kern<<<grid, SLAM_UPDATE_THREADS, sm_f, h->stream>>>(h->soa(h->cur), h->ring(), P, o, K, Rm, noise, ga, nullptr,
+                                                                     pr, Pgl, h->fb_list, h->fb_count);
                 KCHECK();
                 LAUNCHED(h, SLAMGPU_T_UPDATE);
                 if (gauss_in_kernel) {

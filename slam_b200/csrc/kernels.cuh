@@ -274,6 +274,34 @@ __device__ __forceinline__ void stage_obs_fs2(unsigned char *base, const ObsSet 
 }
 #define SLAM_OBS_FS2_SMEM(K) ((2 * sizeof(unsigned long long) + 2 * sizeof(float2)) * (K))
 
+// The same observation set as the fast FastSLAM2 update kernel wants it: physical ROW NUMBERS instead of 64-bit element
+// offsets (an address is then base + row * pitch, one 32 x 32 + 64-bit multiply-add per array instead of a 64-bit add
+// and two 64-bit shifted adds; P * 16 < 2^32 is checked by slamgpu_create), and what pass 2 reads per observation in
+// ONE 16-byte word: (z_range, sin z_b, cos z_b, destination row).  Same footprint as stage_obs_fs2 (32 B / observation).
+template <bool REMAP>
+__device__ __forceinline__ void stage_obs_fast(unsigned char *base, const ObsSet &o, int K, float4 *&sp2, uint2 *&srow,
+                                               float2 *&sz) {
+    sp2 = reinterpret_cast<float4 *>(base);
+    srow = reinterpret_cast<uint2 *>(sp2 + K);
+    sz = reinterpret_cast<float2 *>(srow + K);
+    for (int i = threadIdx.x; i < K; i += blockDim.x) {
+        const float2 z = o.z[i];
+        sz[i] = z;
+        float sb, cb;
+        sincosf(z.y, &sb, &cb);
+        const unsigned rs = (unsigned) o.row[i], rd = (unsigned) (REMAP ? o.row_dst[i] : o.row[i]);
+        sp2[i] = make_float4(z.x, sb, cb, __uint_as_float(rd));
+        srow[i] = make_uint2(rs, rd);
+    }
+    __syncthreads();
+}
+// base + row * pitch in one 32 x 32 + 64-bit multiply-add (IMAD.WIDE.U32)
+__device__ __forceinline__ const char *row_addr(const char *base, unsigned row, unsigned pitch) {
+    unsigned long long a;
+    asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(a) : "r"(row), "r"(pitch), "l"((unsigned long long) base));
+    return reinterpret_cast<const char *>(a);
+}
+
 // anc: the resample's keep[] (or a composed ancestor map) for this device's slots; -1 means "the last particle"
 // exactly as in k_gather_pose (core.cpp:800-806 leaves -1 where select ran past the CDF).
 __device__ __forceinline__ long long remap_column(const int *__restrict__ anc, size_t p, long long n_global) {
@@ -392,9 +420,12 @@ __device__ __forceinline__ void gauss_arrived_load(const GaussArrival &ga, const
     }
 }
 
-// REMAP: 0 = every observed row is current; 1 = some are stale (checked per row: soff != doff); 2 = ALL K are stale —
-// the step after a resample, the common case — so the per-row check and the second pair of copies drop out.
-template <int REMAP>
+// REMAP: 0 = every observed row is current; 1 = some are stale (checked per row: source row != destination row); 2 = ALL
+// K are stale — the step after a resample, the common case — so the per-row check and the second pair of copies drop
+// out.  KFULL: K is a multiple of the ring depth (and >= it), so the "is there a row i" tests of the unrolled walk drop
+// out and "is there a row to prefetch" is one test per D rows.  The kernel is fp32-issue bound (ncu r02: issue slots
+// 83 % busy), so integer bookkeeping per particle-landmark is paid for in update time one for one.
+template <int REMAP, bool KFULL>
 __global__ void __launch_bounds__(SLAM_UPDATE_THREADS, 7) k_fs2_update_fast(PoseSoA s, MapRing m, size_t P, ObsSet o, int K,
                                                                          float4 Rm, const NoiseSrc noise, GaussArrival ga,
                                                                          const int *__restrict__ anc, PeerRows pr,
@@ -403,33 +434,51 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS, 7) k_fs2_update_fast(Pose
     constexpr int D = SLAM_RING_DEPTH, T = SLAM_UPDATE_THREADS;
     float4 *const ring_cov = reinterpret_cast<float4 *>(slam_smem) + threadIdx.x;                // slot s at [s * T]
     float2 *const ring_mean = reinterpret_cast<float2 *>(reinterpret_cast<float4 *>(slam_smem) + D * T) + threadIdx.x;
-    float2 *sz, *ssc;
-    unsigned long long *soff, *doff;
-    stage_obs_fs2<(REMAP != 0)>(slam_smem + (sizeof(float4) + sizeof(float2)) * D * T, o, K, P, sz, soff, doff, ssc);
+    float4 *sp2;
+    uint2 *srow;
+    float2 *sz;
+    stage_obs_fast<(REMAP != 0)>(slam_smem + (sizeof(float4) + sizeof(float2)) * D * T, o, K, sp2, srow, sz);
     const unsigned blk = REMAP ? spread_block(blockIdx.x, gridDim.x, pr.spread, SLAM_SPREAD_CHUNK_SLOTS / T) : blockIdx.x;
     const size_t p = (size_t) blk * blockDim.x + threadIdx.x;
     if (p >= P) return;
-    const float2 *const mean_p = m.mean + p;
-    const float4 *const cov_p = m.cov + p;
+    // row r of this particle's column sits at base + r * pitch (bytes)
+    const unsigned pitch_m = (unsigned) (P * sizeof(float2)), pitch_c = (unsigned) (P * sizeof(float4));
+    const char *const mean_b = reinterpret_cast<const char *>(m.mean + p);
+    const char *const cov_b = reinterpret_cast<const char *>(m.cov + p);
     // a stale row (REMAP) is read at the ancestor's column, on whichever rank holds it
-    const float2 *smean = mean_p;
-    const float4 *scov = cov_p;
-    if (REMAP) remap_source(pr, remap_column(anc, p, n_global), P, smean, scov);
+    const char *smean_b = mean_b, *scov_b = cov_b;
+    if (REMAP) {
+        const float2 *smean;
+        const float4 *scov;
+        remap_source(pr, remap_column(anc, p, n_global), P, smean, scov);
+        smean_b = reinterpret_cast<const char *>(smean);
+        scov_b = reinterpret_cast<const char *>(scov);
+    }
     // row i goes in flight into ring slot `slot`: its own column, or (stale) the ancestor's, then through L1 as well
     auto fetch = [&](int i, int slot) {
-        const unsigned long long so = soff[i];
-        if (REMAP == 2 || (REMAP == 1 && so != doff[i])) {
-            cp_async_8(ring_mean + slot * T, smean + so);
-            cp_async_16_ca(ring_cov + slot * T, scov + so);
+        if (REMAP == 2) {
+            const unsigned r = srow[i].x;
+            cp_async_8(ring_mean + slot * T, row_addr(smean_b, r, pitch_m));
+            cp_async_16_ca(ring_cov + slot * T, row_addr(scov_b, r, pitch_c));
+        } else if (REMAP == 1) {
+            const uint2 rr = srow[i];
+            if (rr.x != rr.y) {
+                cp_async_8(ring_mean + slot * T, row_addr(smean_b, rr.x, pitch_m));
+                cp_async_16_ca(ring_cov + slot * T, row_addr(scov_b, rr.x, pitch_c));
+            } else {
+                cp_async_8(ring_mean + slot * T, row_addr(mean_b, rr.x, pitch_m));
+                cp_async_16(ring_cov + slot * T, row_addr(cov_b, rr.x, pitch_c));
+            }
         } else {
-            cp_async_8(ring_mean + slot * T, mean_p + so);
-            cp_async_16(ring_cov + slot * T, cov_p + so);
+            const unsigned r = srow[i].x;
+            cp_async_8(ring_mean + slot * T, row_addr(mean_b, r, pitch_m));
+            cp_async_16(ring_cov + slot * T, row_addr(cov_b, r, pitch_c));
         }
     };
     // the first D-1 rows go in flight before anything else is looked at
 #pragma unroll
     for (int j = 0; j < D - 1; j++) {
-        if (j < K) fetch(j, j);
+        if (KFULL || j < K) fetch(j, j);
         cp_async_commit();
     }
     const float R[4] = {Rm.x, Rm.y, Rm.z, Rm.w};
@@ -447,16 +496,18 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS, 7) k_fs2_update_fast(Pose
     // pass 1: proposal (read only), sequential over the observations (fastslam2.cpp:314-350); row i sits in slot i % D
     float xf[2], Pf[4];
     for (int i0 = 0; i0 < K; i0 += D) {
+        const bool more = i0 + D < K;  // KFULL: rows i0 + D .. i0 + 2D - 1 exist
 #pragma unroll
         for (int sl = 0; sl < D; sl++) {
             const int i = i0 + sl;
-            if (i < K) {
+            if (KFULL || i < K) {
                 const int j = i + D - 1;
-                if (j < K) fetch(j, (sl + D - 1) % D);
+                if (KFULL ? (sl == 0 || more) : (j < K)) fetch(j, (sl + D - 1) % D);
                 cp_async_commit();
                 cp_async_wait<D - 1>();  // one group per row: all but the newest D-1 have landed, row i among them
                 lm_load_at(ring_mean + sl * T, ring_cov + sl * T, xf, Pf);
-                const float z[2] = {sz[i].x, sz[i].y};
+                const float2 zi = sz[i];
+                const float z[2] = {zi.x, zi.y};
                 proposal_step_fast(x, pi, R, xf, Pf, z);
             }
         }
@@ -473,19 +524,21 @@ __global__ void __launch_bounds__(SLAM_UPDATE_THREADS, 7) k_fs2_update_fast(Pose
     // recently are the ones most likely still in L2 (a forward walk is the LRU worst case).
     float like = 1.0f;
     for (int i0 = ((K - 1) / D) * D; i0 >= 0; i0 -= D) {
+        const bool more = i0 >= D;  // rows i0 - D .. i0 - 1 exist
 #pragma unroll
         for (int sl = D - 1; sl >= 0; sl--) {
             const int i = i0 + sl;
-            if (i < K) {
+            if (KFULL || i < K) {
                 cp_async_wait<D - 1>();
                 lm_load_at(ring_mean + sl * T, ring_cov + sl * T, xf, Pf);
-                const unsigned long long off = doff[i];
-                if (i - D >= 0) fetch(i - D, sl);  // the slot just read takes row i - D
+                const float4 ob = sp2[i];  // z_range, sin z_b, cos z_b, destination row
+                if (more) fetch(i - D, sl);  // the slot just read takes row i - D
                 cp_async_commit();
-                const float2 sc = ssc[i];
-                like = like * likelihood_and_feature_update_fast(xs, sth, cth, R, xf, Pf, sz[i].x, sc.x, sc.y);
-                __stcs(m.mean + p + off, make_float2(xf[0], xf[1]));
-                __stcs(m.cov + p + off, make_float4(Pf[0], Pf[2], Pf[1], Pf[3]));
+                like = like * likelihood_and_feature_update_fast(xs, sth, cth, R, xf, Pf, ob.x, ob.y, ob.z);
+                const unsigned rd = __float_as_uint(ob.w);
+                __stcs(reinterpret_cast<float2 *>(const_cast<char *>(row_addr(mean_b, rd, pitch_m))), make_float2(xf[0], xf[1]));
+                __stcs(reinterpret_cast<float4 *>(const_cast<char *>(row_addr(cov_b, rd, pitch_c))),
+                       make_float4(Pf[0], Pf[2], Pf[1], Pf[3]));
             }
         }
     }

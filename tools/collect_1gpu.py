@@ -18,7 +18,8 @@ def last_json(path):
 def main():
     for f in ("r02_bench_1gpu.json", "r02_bench_1gpu_200steps.json", "r02_bench_reference_arm.json",
               "r02_bench_nf4096_1gpu.json", "r02_fs1_secondary.json", "r02_launches.csv", "r02_gpu_tests.log"):
-        shutil.copy(os.path.join(OUT, f), os.path.join(PROF, f))
+        if os.path.exists(os.path.join(OUT, f)):  # (a partial re-run, tools/run_profile_1gpu.sh, brings only some of them)
+            shutil.copy(os.path.join(OUT, f), os.path.join(PROF, f))
     # ncu summaries
     txt = subprocess.run(["python", os.path.join(ROOT, "tools", "ncu_summary.py"), os.path.join(OUT, "r02_prof.ncu-rep")],
                          capture_output=True, text=True).stdout
@@ -53,6 +54,11 @@ def main():
               open(os.path.join(PROF, "r02_fs2_update_traffic.json"), "w"), indent=1)
     # parity errors
     mx, n = collections.defaultdict(lambda: collections.defaultdict(float)), collections.Counter()
+    if not os.path.exists(os.path.join(OUT, "r02_parity_errors.log")):
+        for t in traffic:
+            print(t)
+        print(dict(seen))
+        return
     for line in open(os.path.join(OUT, "r02_parity_errors.log")):
         d = json.loads(line)
         key = d["context"] or d["what"].split(":")[0][:40]
