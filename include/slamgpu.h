@@ -63,7 +63,7 @@ extern "C" {
 typedef struct slamgpu slamgpu_t;
 
 typedef struct slamgpu_config {
-    int64_t n_particles; /* NPARTICLES held by THIS handle (the local shard when sharded) */
+    int64_t n_particles; /* NPARTICLES held by THIS handle (the local shard when sharded); 1 .. 2^28 - 1 */
     int32_t nf_cap;      /* landmark rows reserved per particle */
     int32_t method;      /* SLAMGPU_FASTSLAM1 / SLAMGPU_FASTSLAM2  (SLAMBackendApplication.cpp:26-29) */
     float wheel_base;    /* WHEELBASE  (fastslam2wrapper.cpp:18-23) */
